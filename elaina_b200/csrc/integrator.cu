@@ -1,0 +1,534 @@
+// Problem + integrator objects and the wavefront walk kernels (uniform integrator).
+//
+// Wavefront scheme (replaces solveImpl, integrator/uniform/integrator.cu:528-623):
+//   reference:  for spp: for depth: 1 single-thread reset kernel + 3..5 full-frame stage kernels, W*H threads each,
+//               one global atomic per pushed item, queues in managed memory.
+//   here:       for each batch of S samples-per-pixel: for depth: ONE fused kernel (walk.cuh) over the compacted queue
+//               of live walks. Persistent grid (multiple of the SM count); each warp claims 32 items at a time with one
+//               atomic (dynamic load balance), keeps the walk state in registers for the whole step, and appends
+//               survivors to the next queue with one warp-aggregated atomic. Depth 0 synthesises its items from
+//               (pixel, sample) -- no generate kernel, no queue read. Per-(slot, pixel) accumulators make the result
+//               independent of scheduling: a pixel's samples of slot s are summed in sample order (== the oracle's
+//               order when S == 1), slots are summed in slot order by the resolve kernel.
+#include "integrator.cuh"
+#include "walk.cuh"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+
+namespace wost
+{
+    constexpr int kWalkBlock = 128;
+
+    WOST_DEV void load_item(const QueueView &q, size_t i, WalkState<2> &w)
+    {
+        const float4 a = q.a[i], b = q.b[i];
+        w.x[0] = a.x, w.x[1] = a.y;
+        w.pixel = __float_as_uint(a.z);
+        const uint32_t sf = __float_as_uint(a.w);
+        w.sample = sf & 0x7fffffffu;
+        w.onN = (sf >> 31) != 0;
+        w.nN[0] = b.x, w.nN[1] = b.y;
+        w.thp = b.z;
+    }
+    WOST_DEV void store_item(const QueueView &q, size_t i, const WalkState<2> &w)
+    {
+        q.a[i] = make_float4(w.x[0], w.x[1], __uint_as_float(w.pixel), __uint_as_float(w.sample | (w.onN ? 0x80000000u : 0u)));
+        q.b[i] = make_float4(w.nN[0], w.nN[1], w.thp, 0.0f);
+    }
+    WOST_DEV void load_item(const QueueView &q, size_t i, WalkState<3> &w)
+    {
+        const float4 a = q.a[i], b = q.b[i];
+        const uint32_t sf = q.c[i];
+        w.x[0] = a.x, w.x[1] = a.y, w.x[2] = a.z;
+        w.thp = a.w;
+        w.nN[0] = b.x, w.nN[1] = b.y, w.nN[2] = b.z;
+        w.pixel = __float_as_uint(b.w);
+        w.sample = sf & 0x7fffffffu;
+        w.onN = (sf >> 31) != 0;
+    }
+    WOST_DEV void store_item(const QueueView &q, size_t i, const WalkState<3> &w)
+    {
+        q.a[i] = make_float4(w.x[0], w.x[1], w.x[2], w.thp);
+        q.b[i] = make_float4(w.nN[0], w.nN[1], w.nN[2], __uint_as_float(w.pixel));
+        q.c[i] = w.sample | (w.onN ? 0x80000000u : 0u);
+    }
+
+    struct StepArgs
+    {
+        QueueView in, out;
+        const int *in_count; // nullptr for depth 0
+        int *out_count;
+        int *cursor;              // claim cursor of this bounce
+        unsigned long long *steps; // walk-step counter
+        const uint32_t *active;
+        int n_active;
+        uint32_t sample0; // first sample of the batch
+        int batch_samples;
+        uint32_t depth;
+        float4 *acc; // [slot][pixel]
+        int npix;
+        int last_depth; // 1: survivors are dropped (depth == maxWalkingDepth-1)
+        int *overflow;
+    };
+
+    template <int D, bool First>
+    __global__ void __launch_bounds__(kWalkBlock) k_step_uniform(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ StepArgs a)
+    {
+        extern __shared__ uint2 smem_stack[];
+        SmemStack st;
+        st.init(smem_stack, a.overflow);
+        const int lane = threadIdx.x & 31;
+        const long long n = First ? (long long)a.n_active * a.batch_samples : (long long)*a.in_count;
+        if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0)
+            atomicAdd(a.steps, (unsigned long long)n);
+        for (;;)
+        {
+            long long base = 0;
+            if (lane == 0)
+                base = (long long)atomicAdd(a.cursor, 32);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base >= n)
+                break;
+            const long long i = base + lane;
+            bool alive = false;
+            WalkState<D> w;
+            if (i < n)
+            {
+                if (First)
+                {
+                    const uint32_t sj = (uint32_t)(i / a.n_active);
+                    w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
+                    w.sample = a.sample0 + sj;
+                    w.x = eval_point(c, w.pixel);
+                    w.thp = 1.0f;
+                    w.onN = false;
+#pragma unroll
+                    for (int k = 0; k < D; ++k)
+                        w.nN[k] = 0.0f;
+                }
+                else
+                    load_item(a.in, (size_t)i, w);
+                PixelAcc acc;
+                acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
+                alive = walk_step_uniform<D>(c, w, a.depth, st, acc);
+                acc.flush();
+            }
+            if (!a.last_depth)
+            {
+                // warp-aggregated append: one atomic per warp
+                const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+                if (mask)
+                {
+                    int slot0 = 0;
+                    if (lane == 0)
+                        slot0 = atomicAdd(a.out_count, __popc(mask));
+                    slot0 = __shfl_sync(0xffffffffu, slot0, 0);
+                    if (alive)
+                        store_item(a.out, (size_t)slot0 + __popc(mask & ((1u << lane) - 1u)), w);
+                }
+            }
+        }
+    }
+
+    // solution/spp -> Film (integrator.cu:614-620): {r,g,b,1, weight 1}; slots are summed in slot order
+    __global__ void k_resolve(int npix, int nslots, const float4 *acc, float inv_spp, const uint32_t *owned_begin_end, float *film)
+    {
+        const int p = blockIdx.x * blockDim.x + threadIdx.x;
+        if (p >= npix)
+            return;
+        float r = 0.0f, g = 0.0f, b = 0.0f;
+        for (int s = 0; s < nslots; ++s)
+        {
+            const float4 v = acc[(size_t)s * npix + p];
+            r = r + v.x;
+            g = g + v.y;
+            b = b + v.z;
+        }
+        float *f = film + (size_t)p * 5;
+        f[0] = dm_div(r, inv_spp);
+        f[1] = dm_div(g, inv_spp);
+        f[2] = dm_div(b, inv_spp);
+        f[3] = 1.0f;
+        f[4] = 1.0f;
+    }
+
+    // renderDirichletSDF / renderSilhouetteSDF / renderSource (integrator/common.h:51-163)
+    template <int D>
+    __global__ void __launch_bounds__(kWalkBlock) k_render_channel(const __grid_constant__ WalkCtx<D> c, int channel, int npix, float *film, int *overflow)
+    {
+        extern __shared__ uint2 smem_stack[];
+        SmemStack st;
+        st.init(smem_stack, overflow);
+        for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x)
+        {
+            const Vec<D> x = eval_point(c, (uint32_t)p);
+            float v[3] = {0.0f, 0.0f, 0.0f};
+            if (channel == WOST_CH_DIRICHLET_SDF)
+            {
+                float d = dm_inf();
+                if (c.dir.nprims > 0)
+                {
+                    uint32_t pos;
+                    query_nearest(c.dir, x, st, pos, d);
+                }
+                v[0] = v[1] = v[2] = d;
+            }
+            else if (channel == WOST_CH_NEUMANN_SDF)
+            {
+                float d = dm_inf();
+                if (c.neu.nprims > 0)
+                    d = query_silhouette(c.neu, x, false, st);
+                v[0] = v[1] = v[2] = d;
+            }
+            else if (channel == WOST_CH_SOURCE)
+            {
+                if (c.source)
+                {
+                    float w3[3];
+                    w3[0] = x[0], w3[1] = x[1], w3[2] = (D == 3) ? x[D - 1] : 0.0f;
+                    source_lookup(c, w3, v);
+                    v[0] *= c.source_intensity, v[1] *= c.source_intensity, v[2] *= c.source_intensity;
+                }
+            }
+            float *f = film + (size_t)p * 5;
+            f[0] = v[0], f[1] = v[1], f[2] = v[2], f[3] = 1.0f, f[4] = 1.0f;
+        }
+    }
+
+    template <int D>
+    static wost_status solve_uniform(wost_integrator *it, uint64_t *walk_steps)
+    {
+        WalkCtx<D> ctx;
+        it->problem->fill_ctx(ctx);
+        ctx.frame_w = it->s.frame_w;
+        ctx.frame_h = it->s.frame_h;
+        ctx.max_depth = it->s.max_walking_depth;
+        ctx.eps = it->s.epsilon_shell;
+        ctx.seed = it->s.seed;
+        const int S = it->spp_batch;
+        const int spp = it->s.samples_per_pixel;
+        const int maxd = it->s.max_walking_depth;
+        cudaStream_t st = it->stream;
+        const size_t smem = stack_smem_bytes(kWalkBlock);
+        int occ = 1;
+        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_step_uniform<D, false>, kWalkBlock, smem));
+        const int grid_full = sm_count() * std::max(1, occ);
+
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
+        it->launches = 0;
+        if (it->n_active > 0)
+        {
+            for (int s0 = 0; s0 < spp; s0 += S)
+            {
+                const int Sb = std::min(S, spp - s0);
+                WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int) * (size_t)(2 * (maxd + 1)), st));
+                for (int depth = 0; depth < maxd; ++depth)
+                {
+                    StepArgs a;
+                    a.in = QueueView{it->qa[depth & 1].ptr, it->qb[depth & 1].ptr, it->qc[depth & 1].ptr};
+                    a.out = QueueView{it->qa[(depth + 1) & 1].ptr, it->qb[(depth + 1) & 1].ptr, it->qc[(depth + 1) & 1].ptr};
+                    a.in_count = depth == 0 ? nullptr : it->d_counts.ptr + depth;
+                    a.out_count = it->d_counts.ptr + depth + 1;
+                    a.cursor = it->d_counts.ptr + (maxd + 1) + depth;
+                    a.steps = it->d_steps.ptr;
+                    a.active = it->d_active.ptr;
+                    a.n_active = it->n_active;
+                    a.sample0 = (uint32_t)s0;
+                    a.batch_samples = Sb;
+                    a.depth = (uint32_t)depth;
+                    a.acc = it->d_acc.ptr;
+                    a.npix = it->npix;
+                    a.last_depth = (depth == maxd - 1) ? 1 : 0;
+                    a.overflow = it->d_overflow.ptr;
+                    if (depth == 0)
+                    {
+                        const long long n0 = (long long)it->n_active * Sb;
+                        const int grid = (int)std::min<long long>(grid_full, (n0 + kWalkBlock - 1) / kWalkBlock);
+                        k_step_uniform<D, true><<<std::max(1, grid), kWalkBlock, smem, st>>>(ctx, a);
+                    }
+                    else
+                        k_step_uniform<D, false><<<grid_full, kWalkBlock, smem, st>>>(ctx, a);
+                    ++it->launches;
+                }
+            }
+        }
+        k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
+        ++it->launches;
+        WOST_CUDA_TRY(cudaGetLastError());
+        unsigned long long h_steps = 0;
+        int h_over = 0;
+        WOST_CUDA_TRY(cudaMemcpyAsync(&h_steps, it->d_steps.ptr, sizeof(h_steps), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaMemcpyAsync(&h_over, it->d_overflow.ptr, sizeof(int), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaEventRecord(it->ev1, st));
+        WOST_CUDA_TRY(cudaStreamSynchronize(st));
+        if (walk_steps)
+            *walk_steps = h_steps;
+        if (h_over)
+        {
+            cudaMemsetAsync(it->d_overflow.ptr, 0, sizeof(int), st);
+            set_last_error("LBVH traversal stack overflow during solve");
+            return WOST_ERR_OVERFLOW;
+        }
+        return WOST_OK;
+    }
+} // namespace wost
+
+using namespace wost;
+
+extern "C"
+{
+    wost_status wost_problem_create(const wost_problem_desc *d, wost_problem **out)
+    {
+        if (!d || !out || (d->dim != 2 && d->dim != 3))
+        {
+            set_last_error("wost_problem_create: invalid argument");
+            return WOST_ERR_INVALID;
+        }
+        if ((d->dirichlet && d->dirichlet->dim != d->dim) || (d->neumann && d->neumann->dim != d->dim))
+        {
+            set_last_error("wost_problem_create: scene dimensionality mismatch");
+            return WOST_ERR_INVALID;
+        }
+        wost_problem *p = new wost_problem();
+        p->dim = d->dim;
+        cudaGetDevice(&p->device);
+        p->dirichlet = d->dirichlet;
+        p->neumann = d->neumann;
+        p->desc = *d;
+        auto fail = [&](wost_status rc, const char *msg)
+        {
+            set_last_error(msg);
+            delete p;
+            return rc;
+        };
+        if (d->dirichlet && d->color_dirichlet)
+        {
+            if (d->n_color_dirichlet < d->dirichlet->nverts)
+                return fail(WOST_ERR_INVALID, "wost_problem_create: fewer Dirichlet colour pairs than vertices");
+            if (p->d_color_dir.upload(d->color_dirichlet, (size_t)d->n_color_dirichlet * 6) != cudaSuccess)
+                return fail(WOST_ERR_CUDA, "wost_problem_create: colour upload failed");
+        }
+        if (d->neumann && d->color_neumann)
+        {
+            if (d->n_color_neumann < d->neumann->nverts)
+                return fail(WOST_ERR_INVALID, "wost_problem_create: fewer Neumann colour pairs than vertices");
+            if (p->d_color_neu.upload(d->color_neumann, (size_t)d->n_color_neumann * 6) != cudaSuccess)
+                return fail(WOST_ERR_CUDA, "wost_problem_create: colour upload failed");
+            for (size_t i = 0; i < (size_t)d->n_color_neumann * 6; ++i)
+                if (d->color_neumann[i] != 0.0f)
+                {
+                    p->neumann_flux_enabled = true;
+                    break;
+                }
+            if (d->neumann_intensity == 0.0f)
+                p->neumann_flux_enabled = false;
+        }
+        if (d->source)
+        {
+            const size_t n = (size_t)d->source_dims[0] * d->source_dims[1] * d->source_dims[2] * 3;
+            if (n == 0 || !(d->source_voxel > 0.0f))
+                return fail(WOST_ERR_INVALID, "wost_problem_create: bad source grid");
+            if (p->d_source.upload(d->source, n) != cudaSuccess)
+                return fail(WOST_ERR_CUDA, "wost_problem_create: source upload failed");
+        }
+        if (d->mask)
+        {
+            p->mask_w = d->mask_w;
+            p->mask_h = d->mask_h;
+            if (p->d_mask.upload(d->mask, (size_t)d->mask_w * d->mask_h) != cudaSuccess)
+                return fail(WOST_ERR_CUDA, "wost_problem_create: mask upload failed");
+        }
+        p->desc.color_dirichlet = nullptr;
+        p->desc.color_neumann = nullptr;
+        p->desc.source = nullptr;
+        if (cudaDeviceSynchronize() != cudaSuccess)
+            return fail(WOST_ERR_CUDA, "wost_problem_create: sync failed");
+        // keep the mask on the host for the active-pixel list
+        if (d->mask)
+        {
+            uint8_t *copy = new uint8_t[(size_t)d->mask_w * d->mask_h];
+            memcpy(copy, d->mask, (size_t)d->mask_w * d->mask_h);
+            p->desc.mask = copy;
+        }
+        *out = p;
+        return WOST_OK;
+    }
+    void wost_problem_destroy(wost_problem *p)
+    {
+        if (!p)
+            return;
+        delete[] p->desc.mask;
+        delete p;
+    }
+
+    wost_status wost_integrator_create(wost_problem *problem, const wost_settings *settings, int kind, wost_integrator **out)
+    {
+        if (!problem || !settings || !out)
+        {
+            set_last_error("wost_integrator_create: invalid argument");
+            return WOST_ERR_INVALID;
+        }
+        if (kind != WOST_UNIFORM)
+        {
+            set_last_error("wost_integrator_create: integrator kind not available in this build");
+            return WOST_ERR_UNSUPPORTED;
+        }
+        const wost_settings &s = *settings;
+        if (s.frame_w <= 0 || s.frame_h <= 0 || s.max_walking_depth <= 0 || s.samples_per_pixel <= 0)
+        {
+            set_last_error("wost_integrator_create: bad settings");
+            return WOST_ERR_INVALID;
+        }
+        if (problem->desc.mask && (problem->mask_w != s.frame_w || problem->mask_h != s.frame_h))
+        {
+            // the reference reads a 1024^2 default mask out of bounds for larger frames (core/problem.cu:245-247)
+            set_last_error("wost_integrator_create: mask size differs from frame size");
+            return WOST_ERR_INVALID;
+        }
+        wost_integrator *it = new wost_integrator();
+        it->problem = problem;
+        it->s = s;
+        it->kind = kind;
+        it->dim = problem->dim;
+        cudaGetDevice(&it->device);
+        it->npix = s.frame_w * s.frame_h;
+        // shard: contiguous pixel range and/or interleaved row tiles
+        int pb = s.pixel_begin, pe = s.pixel_end > 0 ? s.pixel_end : it->npix;
+        pb = std::max(0, std::min(pb, it->npix));
+        pe = std::max(pb, std::min(pe, it->npix));
+        std::vector<uint32_t> active;
+        active.reserve(pe - pb);
+        const uint8_t *mask = problem->desc.mask;
+        for (int p = pb; p < pe; ++p)
+        {
+            if (mask && !mask[p])
+                continue;
+            if (s.pixel_stride_rows > 0 && s.num_shards > 1)
+            {
+                const int row = p / s.frame_w;
+                if ((row / s.pixel_stride_rows) % s.num_shards != s.shard)
+                    continue;
+            }
+            active.push_back((uint32_t)p);
+        }
+        it->n_active = (int)active.size();
+        int S = s.spp_batch;
+        if (S <= 0)
+        {
+            // auto: keep ~16M walks in flight (queues 2 x 32..36 B/item + 16 B/slot-pixel accumulators)
+            const long long target = 16ll << 20;
+            S = (int)std::max<long long>(1, target / std::max(1, it->n_active));
+        }
+        S = std::max(1, std::min(S, s.samples_per_pixel));
+        it->spp_batch = S;
+        it->queue_capacity = (size_t)std::max(1, it->n_active) * S;
+        auto fail = [&](const char *msg)
+        {
+            set_last_error(std::string(msg) + ": " + cudaGetErrorString(cudaGetLastError()));
+            delete it;
+            return WOST_ERR_CUDA;
+        };
+        if (it->d_active.upload(active.data(), active.size()) != cudaSuccess)
+            return fail("active pixel upload");
+        for (int i = 0; i < 2; ++i)
+        {
+            if (it->qa[i].alloc(it->queue_capacity) != cudaSuccess || it->qb[i].alloc(it->queue_capacity) != cudaSuccess)
+                return fail("queue allocation");
+            if (it->dim == 3 && it->qc[i].alloc(it->queue_capacity) != cudaSuccess)
+                return fail("queue allocation");
+        }
+        if (it->d_counts.alloc((size_t)2 * (s.max_walking_depth + 1)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
+            it->d_acc.alloc((size_t)S * it->npix) != cudaSuccess || it->d_overflow.alloc(1) != cudaSuccess)
+            return fail("buffer allocation");
+        for (int c = 0; c < WOST_CH_COUNT; ++c)
+        {
+            if (it->film[c].alloc((size_t)it->npix * 5) != cudaSuccess)
+                return fail("film allocation");
+            cudaMemset(it->film[c].ptr, 0, sizeof(float) * (size_t)it->npix * 5);
+        }
+        cudaMemset(it->d_overflow.ptr, 0, sizeof(int));
+        if (cudaStreamCreateWithFlags(&it->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&it->ev0) != cudaSuccess ||
+            cudaEventCreate(&it->ev1) != cudaSuccess)
+            return fail("stream/event creation");
+        if (cudaDeviceSynchronize() != cudaSuccess)
+            return fail("sync");
+        *out = it;
+        return WOST_OK;
+    }
+    void wost_integrator_destroy(wost_integrator *it) { delete it; }
+
+    wost_status wost_solve(wost_integrator *it, uint64_t *ms, uint64_t *walk_steps, float *device_ms)
+    {
+        if (!it)
+            return WOST_ERR_INVALID;
+        const auto t0 = std::chrono::high_resolution_clock::now();
+        WOST_CUDA_TRY(cudaEventRecord(it->ev0, it->stream));
+        wost_status rc = (it->dim == 2) ? solve_uniform<2>(it, walk_steps) : solve_uniform<3>(it, walk_steps);
+        if (rc != WOST_OK)
+            return rc;
+        const auto t1 = std::chrono::high_resolution_clock::now();
+        if (ms)
+            *ms = (uint64_t)std::chrono::duration_cast<std::chrono::milliseconds>(t1 - t0).count();
+        if (device_ms)
+        {
+            float f = 0.0f;
+            WOST_CUDA_TRY(cudaEventElapsedTime(&f, it->ev0, it->ev1));
+            *device_ms = f;
+        }
+        return WOST_OK;
+    }
+
+    wost_status wost_render_channel(wost_integrator *it, int channel)
+    {
+        if (!it || channel <= WOST_CH_SOLUTION || channel >= WOST_CH_COUNT)
+        {
+            set_last_error("wost_render_channel: invalid channel");
+            return WOST_ERR_INVALID;
+        }
+        const size_t smem = stack_smem_bytes(kWalkBlock);
+        const int grid = std::max(1, std::min(div_up(it->npix, kWalkBlock), sm_count() * 8));
+        if (it->dim == 2)
+        {
+            WalkCtx<2> ctx;
+            it->problem->fill_ctx(ctx);
+            ctx.frame_w = it->s.frame_w, ctx.frame_h = it->s.frame_h, ctx.max_depth = it->s.max_walking_depth, ctx.eps = it->s.epsilon_shell, ctx.seed = it->s.seed;
+            k_render_channel<2><<<grid, kWalkBlock, smem, it->stream>>>(ctx, channel, it->npix, it->film[channel].ptr, it->d_overflow.ptr);
+        }
+        else
+        {
+            WalkCtx<3> ctx;
+            it->problem->fill_ctx(ctx);
+            ctx.frame_w = it->s.frame_w, ctx.frame_h = it->s.frame_h, ctx.max_depth = it->s.max_walking_depth, ctx.eps = it->s.epsilon_shell, ctx.seed = it->s.seed;
+            k_render_channel<3><<<grid, kWalkBlock, smem, it->stream>>>(ctx, channel, it->npix, it->film[channel].ptr, it->d_overflow.ptr);
+        }
+        WOST_CUDA_TRY(cudaGetLastError());
+        WOST_CUDA_TRY(cudaStreamSynchronize(it->stream));
+        return WOST_OK;
+    }
+
+    wost_status wost_film_download(wost_integrator *it, int channel, float *out)
+    {
+        if (!it || !out || channel < 0 || channel >= WOST_CH_COUNT)
+            return WOST_ERR_INVALID;
+        WOST_CUDA_TRY(cudaMemcpyAsync(out, it->film[channel].ptr, sizeof(float) * (size_t)it->npix * 5, cudaMemcpyDeviceToHost, it->stream));
+        WOST_CUDA_TRY(cudaStreamSynchronize(it->stream));
+        return WOST_OK;
+    }
+    wost_status wost_film_device_ptr(wost_integrator *it, int channel, void **d_ptr)
+    {
+        if (!it || !d_ptr || channel < 0 || channel >= WOST_CH_COUNT)
+            return WOST_ERR_INVALID;
+        *d_ptr = it->film[channel].ptr;
+        return WOST_OK;
+    }
+    wost_status wost_last_launch_count(wost_integrator *it, uint64_t *kernel_launches)
+    {
+        if (!it || !kernel_launches)
+            return WOST_ERR_INVALID;
+        *kernel_launches = it->launches;
+        return WOST_OK;
+    }
+}

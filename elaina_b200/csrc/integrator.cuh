@@ -1,0 +1,51 @@
+// Host-side integrator object behind `wost_integrator`.
+#pragma once
+#include "problem.cuh"
+
+namespace wost
+{
+    // Work queue of walk states: "SoA of 128-bit lanes". Replaces WorkQueue<T>/SOA<T>
+    // (integrator/uniform/workqueue.h:32-69, util/soac.cpp:302-508): one float4 column per 16 bytes of state, so a warp
+    // moves 512 contiguous bytes per instruction; slots are claimed with ONE atomic per warp (ballot + popc), not one
+    // per item, and the queue of bounce d+1 is written compacted, so later bounces only touch live walks.
+    //   2D: a = {x, y, bits(pixel), bits(sample | onN << 31)}   b = {nx, ny, thp, 0}
+    //   3D: a = {x, y, z, thp}   b = {nx, ny, nz, bits(pixel)}   c = sample | onN << 31
+    struct QueueView
+    {
+        float4 *a;
+        float4 *b;
+        uint32_t *c;
+    };
+}
+
+struct wost_integrator
+{
+    wost_problem *problem = nullptr; // not owned
+    wost_settings s;
+    int kind = 0, dim = 0, device = 0;
+    int npix = 0;
+    int n_active = 0;  // pixels of this shard that pass the mask
+    int spp_batch = 1; // S: samples of every pixel in flight per wavefront
+    size_t queue_capacity = 0;
+    wost::DevBuf<uint32_t> d_active;
+    wost::DevBuf<float4> qa[2], qb[2];
+    wost::DevBuf<uint32_t> qc[2];
+    wost::DevBuf<int> d_counts; // [0..max_depth]: items of bounce d; [max_depth+1 ..]: claim cursors
+    wost::DevBuf<unsigned long long> d_steps;
+    wost::DevBuf<float4> d_acc; // [slot][pixel] rgb accumulators
+    wost::DevBuf<float> film[WOST_CH_COUNT];
+    wost::DevBuf<int> d_overflow;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint64_t launches = 0;
+
+    ~wost_integrator()
+    {
+        if (ev0)
+            cudaEventDestroy(ev0);
+        if (ev1)
+            cudaEventDestroy(ev1);
+        if (stream)
+            cudaStreamDestroy(stream);
+    }
+};

@@ -1,0 +1,571 @@
+// SNCH-LBVH device representation and traversal (sm_100a).
+//
+// What is kept from the reference (ext/lbvh/include/snch_lbvh): the tree itself -- Morton order, Karras
+// topology, boxes, cones -- and the exact visit order of each query, so that indices and distances are
+// bit-identical (ties at shared polyline vertices are resolved by visit order, core/query.cuh:279-314).
+// What is re-designed for B200:
+//   * one fused record per INTERNAL node holding both children's boxes (and cones, for silhouette queries)
+//     plus both child references: a visit is 3-6 independent 128-bit loads from ONE 48..96 B record instead of
+//     the reference's 5-7 dependent scattered loads (node 16 B -> 2 child boxes -> 2 child nodes -> object -> vertices);
+//   * leaves reference Morton-ordered inline primitive / silhouette records (no index indirection);
+//   * the traversal stack lives in shared memory, one bank-conflict-free column per lane ([level][lane]),
+//     not in a 512 B local-memory array (core/query.cuh:250).
+#pragma once
+#include "geom.cuh"
+
+namespace wost
+{
+    template <int D>
+    struct TNode; // nearest / ray / sphere-descent record
+    template <>
+    struct __align__(16) TNode<2>
+    {
+        float lb[4]; // up.x up.y lo.x lo.y
+        float rb[4];
+        uint32_t lref, rref, pad0, pad1; // child refs: internal index, or leaf position | kLeafFlag
+    };
+    template <>
+    struct __align__(16) TNode<3>
+    {
+        float lb[6]; // up.xyz lo.xyz
+        float rb[6];
+        uint32_t lref, rref, pad0, pad1;
+    };
+    static_assert(sizeof(TNode<2>) == 48 && sizeof(TNode<3>) == 64, "TNode layout");
+
+    template <int D>
+    struct CNode; // cones of both children (silhouette queries read TNode + CNode)
+    template <>
+    struct __align__(16) CNode<2>
+    {
+        float lc[4]; // axis.x axis.y half_angle radius
+        float rc[4];
+    };
+    template <>
+    struct __align__(16) CNode<3>
+    {
+        float lc[5]; // axis.xyz half_angle radius
+        float rc[5];
+        float pad[2];
+    };
+    static_assert(sizeof(CNode<2>) == 32 && sizeof(CNode<3>) == 48, "CNode layout");
+
+    template <int D>
+    struct LeafPrim;
+    template <>
+    struct __align__(16) LeafPrim<2>
+    {
+        float p[4]; // pa.xy pb.xy
+    };
+    template <>
+    struct __align__(16) LeafPrim<3>
+    {
+        float p[9]; // pa pb pc
+        uint32_t obj;
+        float pad[2];
+    };
+    static_assert(sizeof(LeafPrim<2>) == 16 && sizeof(LeafPrim<3>) == 48, "LeafPrim layout");
+
+    template <int D>
+    struct LeafSil;
+    template <>
+    struct __align__(16) LeafSil<2>
+    {
+        float p[2], n0[2], n1[2];
+        uint32_t flags, pad;
+    };
+    template <>
+    struct __align__(16) LeafSil<3>
+    {
+        float pa[3], pb[3], n0[3], n1[3];
+        uint32_t flags, pad[3];
+    };
+    static_assert(sizeof(LeafSil<2>) == 32 && sizeof(LeafSil<3>) == 64, "LeafSil layout");
+
+    template <int D>
+    struct DevBVH
+    {
+        int nprims;
+        const TNode<D> *tnodes;     // nprims-1
+        const CNode<D> *cnodes;     // nprims-1
+        const LeafPrim<D> *leaf_prim; // nprims (Morton order)
+        const uint32_t *leaf_obj;   // nprims: original object index of leaf position
+        const LeafSil<D> *leaf_sil; // nprims*D
+        float root_box[2 * D];      // up, lo
+        float root_cone[D + 2];
+    };
+
+    // ---------------------------------------------------------------- 128-bit loads
+    WOST_DEV float4 ldg4(const void *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
+
+    template <int D>
+    struct NodeView
+    {
+        Box<D> lb, rb;
+        uint32_t lref, rref;
+    };
+    WOST_DEV NodeView<2> load_tnode(const TNode<2> *n)
+    {
+        const float4 a = ldg4(n), b = ldg4(reinterpret_cast<const char *>(n) + 16), c = ldg4(reinterpret_cast<const char *>(n) + 32);
+        NodeView<2> v;
+        v.lb.up[0] = a.x, v.lb.up[1] = a.y, v.lb.lo[0] = a.z, v.lb.lo[1] = a.w;
+        v.rb.up[0] = b.x, v.rb.up[1] = b.y, v.rb.lo[0] = b.z, v.rb.lo[1] = b.w;
+        v.lref = __float_as_uint(c.x);
+        v.rref = __float_as_uint(c.y);
+        return v;
+    }
+    WOST_DEV NodeView<3> load_tnode(const TNode<3> *n)
+    {
+        const char *q = reinterpret_cast<const char *>(n);
+        const float4 a = ldg4(q), b = ldg4(q + 16), c = ldg4(q + 32), d = ldg4(q + 48);
+        NodeView<3> v;
+        v.lb.up[0] = a.x, v.lb.up[1] = a.y, v.lb.up[2] = a.z, v.lb.lo[0] = a.w;
+        v.lb.lo[1] = b.x, v.lb.lo[2] = b.y, v.rb.up[0] = b.z, v.rb.up[1] = b.w;
+        v.rb.up[2] = c.x, v.rb.lo[0] = c.y, v.rb.lo[1] = c.z, v.rb.lo[2] = c.w;
+        v.lref = __float_as_uint(d.x);
+        v.rref = __float_as_uint(d.y);
+        return v;
+    }
+    WOST_DEV void load_cnode(const CNode<2> *n, Cone<2> &l, Cone<2> &r)
+    {
+        const float4 a = ldg4(n), b = ldg4(reinterpret_cast<const char *>(n) + 16);
+        l.axis[0] = a.x, l.axis[1] = a.y, l.half_angle = a.z, l.radius = a.w;
+        r.axis[0] = b.x, r.axis[1] = b.y, r.half_angle = b.z, r.radius = b.w;
+    }
+    WOST_DEV void load_cnode(const CNode<3> *n, Cone<3> &l, Cone<3> &r)
+    {
+        const char *q = reinterpret_cast<const char *>(n);
+        const float4 a = ldg4(q), b = ldg4(q + 16), c = ldg4(q + 32);
+        l.axis[0] = a.x, l.axis[1] = a.y, l.axis[2] = a.z, l.half_angle = a.w;
+        l.radius = b.x, r.axis[0] = b.y, r.axis[1] = b.z, r.axis[2] = b.w;
+        r.half_angle = c.x, r.radius = c.y;
+    }
+    WOST_DEV Prim<2> load_prim(const LeafPrim<2> *p)
+    {
+        const float4 a = ldg4(p);
+        Prim<2> r;
+        r.p[0][0] = a.x, r.p[0][1] = a.y, r.p[1][0] = a.z, r.p[1][1] = a.w;
+        return r;
+    }
+    WOST_DEV Prim<3> load_prim(const LeafPrim<3> *p)
+    {
+        const char *q = reinterpret_cast<const char *>(p);
+        const float4 a = ldg4(q), b = ldg4(q + 16), c = ldg4(q + 32);
+        Prim<3> r;
+        r.p[0][0] = a.x, r.p[0][1] = a.y, r.p[0][2] = a.z, r.p[1][0] = a.w;
+        r.p[1][1] = b.x, r.p[1][2] = b.y, r.p[2][0] = b.z, r.p[2][1] = b.w;
+        r.p[2][2] = c.x;
+        return r;
+    }
+    WOST_DEV SilRec<2> load_sil(const LeafSil<2> *p)
+    {
+        const float4 a = ldg4(p), b = ldg4(reinterpret_cast<const char *>(p) + 16);
+        SilRec<2> s;
+        s.p[0] = a.x, s.p[1] = a.y, s.n0[0] = a.z, s.n0[1] = a.w;
+        s.n1[0] = b.x, s.n1[1] = b.y;
+        s.flags = __float_as_uint(b.z);
+        return s;
+    }
+    WOST_DEV SilRec<3> load_sil(const LeafSil<3> *p)
+    {
+        const char *q = reinterpret_cast<const char *>(p);
+        const float4 a = ldg4(q), b = ldg4(q + 16), c = ldg4(q + 32), d = ldg4(q + 48);
+        SilRec<3> s;
+        s.pa[0] = a.x, s.pa[1] = a.y, s.pa[2] = a.z, s.pb[0] = a.w;
+        s.pb[1] = b.x, s.pb[2] = b.y, s.n0[0] = b.z, s.n0[1] = b.w;
+        s.n0[2] = c.x, s.n1[0] = c.y, s.n1[1] = c.z, s.n1[2] = c.w;
+        s.flags = __float_as_uint(d.x);
+        return s;
+    }
+    template <int D>
+    WOST_DEV Box<D> root_box_of(const DevBVH<D> &b)
+    {
+        Box<D> r;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+        {
+            r.up[k] = b.root_box[k];
+            r.lo[k] = b.root_box[D + k];
+        }
+        return r;
+    }
+
+    // ---------------------------------------------------------------- traversal stack
+    // Shared-memory stack, one column per thread: entry(level, tid) = base[level * blockDim + tid].
+    // Consecutive lanes hit consecutive 8-byte slots -> conflict-free. The first kSmemLevels levels live in shared memory, deeper ones
+    // (real scenes need <= 26 in total) spill to local memory; beyond 64 (the reference's limit) a flag is raised.
+    constexpr int kSmemLevels = 24; // short stack in shared memory
+    constexpr int kSpillLevels = 40; // deeper levels spill to local memory (reference limit: 64 in total)
+    struct StackEntry
+    {
+        uint32_t ref;
+        float d;
+    };
+    struct SmemStack
+    {
+        uint2 *base; // column of this thread (already offset by tid)
+        int stride;  // blockDim.x
+        int sp;
+        int *overflow;
+        uint2 spill[kSpillLevels];
+        WOST_DEV void init(uint2 *smem, int *overflow_flag)
+        {
+            base = smem + threadIdx.x;
+            stride = blockDim.x;
+            sp = 0;
+            overflow = overflow_flag;
+        }
+        WOST_DEV void push(uint32_t ref, float d)
+        {
+            const uint2 e = make_uint2(ref, __float_as_uint(d));
+            if (sp < kSmemLevels)
+                base[sp * stride] = e;
+            else if (sp < kSmemLevels + kSpillLevels)
+                spill[sp - kSmemLevels] = e;
+            else
+            {
+                if (overflow)
+                    *overflow = 1;
+                return;
+            }
+            ++sp;
+        }
+        WOST_DEV StackEntry pop()
+        {
+            --sp;
+            const uint2 e = (sp < kSmemLevels) ? base[sp * stride] : spill[sp - kSmemLevels];
+            StackEntry r;
+            r.ref = e.x;
+            r.d = __uint_as_float(e.y);
+            return r;
+        }
+        WOST_DEV bool empty() const { return sp <= 0; }
+    };
+    inline size_t stack_smem_bytes(int block_threads) { return (size_t)block_threads * kSmemLevels * sizeof(uint2); }
+
+    // ---------------------------------------------------------------- closest primitive (core/query.cuh:238-318)
+    // Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]) and the distance.
+    // Visit order mirrors the reference: L handled before R, leaves evaluated immediately, internal children
+    // pushed L then R (R popped first); "<=" keeps the last visited of exact ties.
+    template <int D>
+    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist)
+    {
+        leaf_pos = kInvalid;
+        float best = dm_inf();
+        if (bvh.nprims <= 0)
+        {
+            dist = best;
+            return;
+        }
+        if (bvh.nprims == 1)
+        {
+            const float d = prim_distance(load_prim(bvh.leaf_prim), q);
+            leaf_pos = 0;
+            dist = dm_sqrt(d * d);
+            return;
+        }
+        st.sp = 0;
+        uint32_t node = 0;
+        float node_d = box_mindist(root_box_of(bvh), q);
+        bool have = true;
+        while (true)
+        {
+            if (!have)
+            {
+                if (st.empty())
+                    break;
+                const StackEntry e = st.pop();
+                node = e.ref;
+                node_d = e.d;
+            }
+            have = false;
+            if (node_d > best)
+                continue;
+            const NodeView<D> n = load_tnode(bvh.tnodes + node);
+            const float Lmin = box_mindist(n.lb, q), Rmin = box_mindist(n.rb, q);
+            const float Lmm = box_minmaxdist(n.lb, q), Rmm = box_minmaxdist(n.rb, q);
+            const bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
+            bool pushL = false;
+            if (goL)
+            {
+                if (n.lref & kLeafFlag)
+                {
+                    const uint32_t pos = n.lref & ~kLeafFlag;
+                    float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
+                    d *= d;
+                    if (d <= best)
+                    {
+                        best = d;
+                        leaf_pos = pos;
+                    }
+                }
+                else
+                    pushL = true;
+            }
+            if (goR)
+            {
+                if (n.rref & kLeafFlag)
+                {
+                    const uint32_t pos = n.rref & ~kLeafFlag;
+                    float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
+                    d *= d;
+                    if (d <= best)
+                    {
+                        best = d;
+                        leaf_pos = pos;
+                    }
+                }
+                else
+                {
+                    // R would be pushed last and popped next: keep it in registers
+                    if (pushL)
+                        st.push(n.lref, Lmin);
+                    pushL = false;
+                    node = n.rref;
+                    node_d = Rmin;
+                    have = true;
+                }
+            }
+            if (pushL)
+            {
+                // only L is internal: it is the next pop
+                node = n.lref;
+                node_d = Lmin;
+                have = true;
+            }
+        }
+        dist = dm_sqrt(best);
+    }
+
+    // ---------------------------------------------------------------- closest silhouette (core/query.cuh:325-423)
+    template <int D>
+    WOST_DEV bool leaf_sil_distance(const DevBVH<D> &bvh, uint32_t pos, const Vec<D> &q, float max_r2, float &dist, bool flip)
+    {
+        // scene.cuh:517-541 / 978-1003
+        float maxd = max_r2;
+        bool ret = false;
+#pragma unroll
+        for (int j = 0; j < D; ++j)
+        {
+            const SilRec<D> s = load_sil(bvh.leaf_sil + (size_t)pos * D + j);
+            if (!(s.flags & 1u))
+                continue;
+            if (sil_closest(s, q, maxd, dist, flip))
+            {
+                ret = true;
+                maxd = dist * dist;
+            }
+        }
+        return ret;
+    }
+    template <int D>
+    WOST_DEV float query_silhouette(const DevBVH<D> &bvh, const Vec<D> &q, bool flip, SmemStack &st)
+    {
+        float best = dm_inf();
+        if (bvh.nprims <= 0)
+            return best;
+        if (bvh.nprims == 1)
+        {
+            float d = dm_inf();
+            if (bvh.root_cone[D] >= 0.0f && leaf_sil_distance(bvh, 0, q, dm_inf(), d, flip))
+                best = d;
+            return best;
+        }
+        st.sp = 0;
+        uint32_t node = 0;
+        float node_d = box_mindist(root_box_of(bvh), q);
+        bool have = true;
+        while (true)
+        {
+            if (!have)
+            {
+                if (st.empty())
+                    break;
+                const StackEntry e = st.pop();
+                node = e.ref;
+                node_d = e.d;
+            }
+            have = false;
+            if (node_d > best * best)
+                continue;
+            const NodeView<D> n = load_tnode(bvh.tnodes + node);
+            Cone<D> lc, rc;
+            load_cnode(bvh.cnodes + node, lc, rc);
+            const float Lmin = box_mindist(n.lb, q), Rmin = box_mindist(n.rb, q);
+            const bool hitL = lc.half_angle >= 0.0f && cone_overlap(lc, q, n.lb, Lmin);
+            const bool hitR = rc.half_angle >= 0.0f && cone_overlap(rc, q, n.rb, Rmin);
+            bool pushL = false;
+            if (hitL)
+            {
+                if (n.lref & kLeafFlag)
+                {
+                    float d = dm_inf();
+                    const bool found = leaf_sil_distance(bvh, n.lref & ~kLeafFlag, q, best * best, d, flip);
+                    if (found && d <= best)
+                        best = d;
+                }
+                else
+                    pushL = true;
+            }
+            if (hitR)
+            {
+                if (n.rref & kLeafFlag)
+                {
+                    float d = dm_inf();
+                    const bool found = leaf_sil_distance(bvh, n.rref & ~kLeafFlag, q, best * best, d, flip);
+                    if (found && d <= best)
+                        best = d;
+                }
+                else
+                {
+                    if (pushL)
+                        st.push(n.lref, Lmin);
+                    pushL = false;
+                    node = n.rref;
+                    node_d = Rmin;
+                    have = true;
+                }
+            }
+            if (pushL)
+            {
+                node = n.lref;
+                node_d = Lmin;
+                have = true;
+            }
+        }
+        return best;
+    }
+
+    // ---------------------------------------------------------------- rays (core/query.cuh:79-169)
+    struct RayResult
+    {
+        bool hit;
+        float t, u, v;
+        uint32_t leaf_pos;
+    };
+    template <int D, bool TestOnly>
+    WOST_DEV RayResult query_ray(const DevBVH<D> &bvh, const Ray<D> &r, float max_dist, SmemStack &st)
+    {
+        RayResult res;
+        res.hit = false, res.t = dm_inf(), res.u = 0.0f, res.v = 0.0f, res.leaf_pos = kInvalid;
+        if (bvh.nprims <= 0)
+            return res;
+        float best = dm_inf();
+        st.sp = 0;
+        uint32_t ref = (bvh.nprims == 1) ? kLeafFlag : 0u;
+        float ref_d = dm_inf();
+        bool have = true;
+        while (true)
+        {
+            if (!have)
+            {
+                if (st.empty())
+                    break;
+                const StackEntry e = st.pop();
+                ref = e.ref;
+                ref_d = e.d;
+            }
+            have = false;
+            if (ref_d > best)
+                continue;
+            if (ref & kLeafFlag)
+            {
+                const uint32_t pos = ref & ~kLeafFlag;
+                const Hit h = ray_prim(load_prim(bvh.leaf_prim + pos), r);
+                if (h.hit && h.t < max_dist && h.t < best)
+                {
+                    best = h.t;
+                    res.hit = true;
+                    if (TestOnly)
+                        return res;
+                    res.u = h.u;
+                    res.v = h.v;
+                    res.leaf_pos = pos;
+                }
+            }
+            else
+            {
+                const NodeView<D> n = load_tnode(bvh.tnodes + ref);
+                float Ld = 0.0f, Rd = 0.0f;
+                const bool Lh = ray_box(r, n.lb, max_dist, &Ld);
+                const bool Rh = ray_box(r, n.rb, max_dist, &Rd);
+                if (Lh && Rh)
+                {
+                    uint32_t closer = n.lref, other = n.rref;
+                    if (Rd < Ld)
+                    {
+                        const float t = Ld;
+                        Ld = Rd;
+                        Rd = t;
+                        closer = n.rref;
+                        other = n.lref;
+                    }
+                    st.push(other, Rd);
+                    ref = closer;
+                    ref_d = Ld;
+                    have = true;
+                }
+                else if (Lh)
+                {
+                    ref = n.lref;
+                    ref_d = Ld;
+                    have = true;
+                }
+                else if (Rh)
+                {
+                    ref = n.rref;
+                    ref_d = Rd;
+                    have = true;
+                }
+            }
+        }
+        res.t = best;
+        return res;
+    }
+
+    // ---------------------------------------------------------------- Green-weighted descent (core/sample.cuh:23-92)
+    template <int D>
+    WOST_DEV void sample_in_sphere(const DevBVH<D> &bvh, const Vec<D> &c, float radius, float u, int &leaf_pos, float &pdf_out)
+    {
+        leaf_pos = -1;
+        pdf_out = 0.0f;
+        if (bvh.nprims <= 0)
+            return;
+        uint32_t ref = (bvh.nprims == 1) ? kLeafFlag : 0u;
+        float pdf = 1.0f;
+        for (;;)
+        {
+            if (ref & kLeafFlag)
+            {
+                const uint32_t pos = ref & ~kLeafFlag;
+                const Prim<D> pr = load_prim(bvh.leaf_prim + pos);
+                if (sphere_prim(pr, c, radius))
+                {
+                    leaf_pos = (int)pos;
+                    pdf_out = dm_div(pdf, prim_measure(pr));
+                }
+                return;
+            }
+            const NodeView<D> n = load_tnode(bvh.tnodes + ref);
+            const float Lw = sphere_box(c, radius, n.lb) ? green_weight(c, box_centroid(n.lb)) : 0.0f;
+            const float Rw = sphere_box(c, radius, n.rb) ? green_weight(c, box_centroid(n.rb)) : 0.0f;
+            const float tw = Lw + Rw;
+            if (!(tw > 0))
+                return;
+            const float Lp = dm_div(Lw, tw);
+            if (u < Lp)
+            {
+                u = dm_div(u, Lp);
+                ref = n.lref;
+                pdf = Lp * pdf;
+            }
+            else
+            {
+                const float Rp = 1.0f - Lp;
+                u = dm_div(u - Lp, Rp);
+                ref = n.rref;
+                pdf = Rp * pdf;
+            }
+        }
+    }
+} // namespace wost

@@ -1,0 +1,65 @@
+// Host-side scene object behind the opaque `wost_scene` handle.
+#pragma once
+#include "common.cuh"
+#include "lbvh.cuh"
+
+struct wost_scene
+{
+    int dim = 0;
+    int device = 0;
+    int nverts = 0, nprims = 0, nsil = 0;
+    bool used_morton64 = false;
+    std::vector<float> h_verts; // nverts*dim
+    std::vector<int> h_prims;   // nprims*dim
+    // inputs on device
+    wost::DevBuf<float> d_verts;
+    wost::DevBuf<int> d_prims, d_sil_rec, d_prim_sil;
+    // canonical LBVH (reference layout) -- parity probes + source of the traversal layout
+    wost::DevBuf<wost::Node> d_nodes;
+    wost::DevBuf<float> d_boxes; // num_nodes * 2*dim (up, lo)
+    wost::DevBuf<float> d_cones; // num_nodes * (dim+2)
+    wost::DevBuf<uint32_t> d_morton, d_order;
+    // traversal layout
+    wost::DevBuf<char> d_tnodes, d_cnodes, d_leaf_prim, d_leaf_sil;
+    wost::DevBuf<uint32_t> d_leaf_obj;
+    wost::DevBuf<int> d_overflow;
+    float root_box[6] = {0, 0, 0, 0, 0, 0};
+    float root_cone[5] = {0, 0, 0, 0, 0};
+
+    template <int D>
+    wost::DevBVH<D> view() const
+    {
+        wost::DevBVH<D> b;
+        b.nprims = nprims;
+        b.tnodes = reinterpret_cast<const wost::TNode<D> *>(d_tnodes.ptr);
+        b.cnodes = reinterpret_cast<const wost::CNode<D> *>(d_cnodes.ptr);
+        b.leaf_prim = reinterpret_cast<const wost::LeafPrim<D> *>(d_leaf_prim.ptr);
+        b.leaf_obj = d_leaf_obj.ptr;
+        b.leaf_sil = reinterpret_cast<const wost::LeafSil<D> *>(d_leaf_sil.ptr);
+        for (int k = 0; k < 2 * D; ++k)
+            b.root_box[k] = root_box[k];
+        for (int k = 0; k < D + 2; ++k)
+            b.root_cone[k] = root_cone[k];
+        return b;
+    }
+};
+
+namespace wost
+{
+    template <int D>
+    inline DevBVH<D> empty_bvh()
+    {
+        DevBVH<D> b;
+        b.nprims = 0;
+        b.tnodes = nullptr;
+        b.cnodes = nullptr;
+        b.leaf_prim = nullptr;
+        b.leaf_obj = nullptr;
+        b.leaf_sil = nullptr;
+        for (int k = 0; k < 2 * D; ++k)
+            b.root_box[k] = 0.0f;
+        for (int k = 0; k < D + 2; ++k)
+            b.root_cone[k] = 0.0f;
+        return b;
+    }
+}

@@ -1,0 +1,495 @@
+// One walk-on-stars step as a single fused device function (sm_100a).
+//
+// The reference runs a step as 5-7 separate full-frame kernels that hand work items to each other through
+// managed-memory queues (integrator/uniform/integrator.cu:552-575: separate -> handleBoundary -> sampleSource ->
+// sampleNeumann -> oneStepWalk). Here the whole step -- closest-point query, epsilon-shell test, Dirichlet read-out,
+// silhouette query, star radius, source sample, Neumann boundary sample + visibility ray, direction sample, Neumann
+// ray cast and reflection bookkeeping -- runs on register-resident state; only BVH records are fetched from memory.
+// Semantics (what is computed, in which order contributions reach the pixel accumulator) follow the reference stage
+// by stage; file:line cited at each block. Randomness is the counter-based Philox stream of philox.h.
+#pragma once
+#include "lbvh.cuh"
+#include "philox.h"
+#include "problem.cuh"
+
+namespace wost
+{
+    template <int D>
+    struct WalkState
+    {
+        Vec<D> x;       // current point
+        Vec<D> nN;      // shading normal of the Neumann boundary the point sits on (if onN)
+        float thp;      // throughput (a scalar: every factor applied to it is a scalar, oneStepWalk :521)
+        uint32_t pixel; // pixelId = x + y*W
+        uint32_t sample;
+        bool onN;
+    };
+
+    // core/evaluation_grid.h:27-33 / 60-64
+    template <int D>
+    WOST_DEV Vec<D> eval_point(const WalkCtx<D> &c, uint32_t pixel)
+    {
+        const int px = (int)(pixel % (uint32_t)c.frame_w), py = (int)(pixel / (uint32_t)c.frame_w);
+        const float nx = dm_div(2.0f * (float)px, (float)c.frame_w) + (-1.0f);
+        const float ny = dm_div(2.0f * (float)py, (float)c.frame_h) + (-1.0f);
+        Vec<D> r;
+        if (D == 2)
+        {
+            const float ux = c.grid_up[1], uy = -c.grid_up[0];
+            const float vx = c.grid_up[0], vy = c.grid_up[1];
+            r[0] = c.grid_scale * (nx * ux + ny * vx) + c.grid_pos[0];
+            r[1] = c.grid_scale * (nx * uy + ny * vy) + c.grid_pos[1];
+        }
+        else
+        {
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+                r[k] = c.grid_scale * (nx * c.grid_right[k] + ny * c.grid_up[k]) + c.grid_pos[k];
+        }
+        return r;
+    }
+
+    template <int D>
+    WOST_DEV bool uv_strictly_inside(const float uv[2]) // integrator/uniform/integrator.cu:159-168
+    {
+        if (D == 2)
+            return uv[0] > 0.0f && uv[0] < 1.0f;
+        return uv[0] > 0.0f && uv[1] > 0.0f && uv[0] + uv[1] < 1.0f;
+    }
+    // integrator/common.h:242-260 + krrmath/functors.h:60-95
+    template <int D>
+    WOST_DEV void surface_color(const float *pairs, const int *vidx, int side, const float uv[2], float out[3])
+    {
+        if (!pairs)
+        {
+            out[0] = out[1] = out[2] = 0.0f;
+            return;
+        }
+        const int off = side >= 0 ? 0 : 3;
+        const float *c0 = pairs + (size_t)vidx[0] * 6 + off;
+        const float *c1 = pairs + (size_t)vidx[1] * 6 + off;
+        if (D == 2)
+        {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch)
+                out[ch] = __ldg(c0 + ch) * (1 - uv[0]) + __ldg(c1 + ch) * uv[0];
+        }
+        else
+        {
+            const float *c2 = pairs + (size_t)vidx[D - 1] * 6 + off;
+            const float w = 1 - uv[0] - uv[1];
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch)
+                out[ch] = __ldg(c0 + ch) * w + __ldg(c1 + ch) * uv[0] + __ldg(c2 + ch) * uv[1];
+        }
+    }
+
+    // util/sampling.h:18-33, 68-85
+    WOST_DEV Vec<2> sample_sphere(float u1, float, Vec<2> *)
+    {
+        Vec<2> r;
+        dm_sincos(u1 * DM_2PI, &r[1], &r[0]);
+        return r;
+    }
+    WOST_DEV Vec<3> sample_sphere(float u1, float u2, Vec<3> *)
+    {
+        const float z = 1 - 2 * u1;
+        const float rr = dm_sqrt(1 - z * z);
+        float s, c;
+        dm_sincos(DM_2PI * u2, &s, &c);
+        Vec<3> r;
+        r[0] = rr * c, r[1] = rr * s, r[2] = z;
+        return r;
+    }
+    WOST_DEV Vec<2> sample_hemisphere_local(float u1, float, Vec<2> *)
+    {
+        Vec<2> r;
+        dm_sincos(DM_PI * u1, &r[1], &r[0]);
+        return r;
+    }
+    WOST_DEV Vec<3> sample_hemisphere_local(float u1, float u2, Vec<3> *)
+    {
+        const float z = u1;
+        const float rr = dm_sqrt(dm_max(0.0f, 1.0f - z * z));
+        float s, c;
+        dm_sincos(2.0f * DM_PI * u2, &s, &c);
+        Vec<3> r;
+        r[0] = rr * c, r[1] = rr * s, r[2] = z;
+        return r;
+    }
+    // util/transformation.h:52-67 + util/math_utils.h:141-156
+    WOST_DEV Vec<2> to_world(const Vec<2> &n, const Vec<2> &v)
+    {
+        Vec<2> perp;
+        perp[0] = -n[1], perp[1] = n[0];
+        const float l2 = perp[0] * perp[0] + perp[1] * perp[1];
+        if (l2 > 0.0f)
+        {
+            const float l = dm_sqrt(l2);
+            perp[0] = dm_div(perp[0], l);
+            perp[1] = dm_div(perp[1], l);
+        }
+        Vec<2> r;
+        r[0] = -perp[0] * v[0] + n[0] * v[1];
+        r[1] = -perp[1] * v[0] + n[1] * v[1];
+        return r;
+    }
+    WOST_DEV Vec<3> safe_normalized(const Vec<3> &a)
+    {
+        const float l2 = vdot(a, a);
+        if (!(l2 > 0.0f))
+            return a;
+        const float l = dm_sqrt(l2);
+        Vec<3> r;
+        r[0] = dm_div(a[0], l), r[1] = dm_div(a[1], l), r[2] = dm_div(a[2], l);
+        return r;
+    }
+    WOST_DEV Vec<3> to_world(const Vec<3> &n, const Vec<3> &v)
+    {
+        const float ax = dm_abs(n[0]), ay = dm_abs(n[1]), az = dm_abs(n[2]);
+        const uint32_t uyx = (ax - ay) < 0 ? 1 : 0, uzx = (ax - az) < 0 ? 1 : 0, uzy = (ay - az) < 0 ? 1 : 0;
+        const uint32_t xm = uyx & uzx, ym = (1 ^ xm) & uzy, zm = 1 ^ (xm | ym);
+        Vec<3> a;
+        a[0] = (float)xm, a[1] = (float)ym, a[2] = (float)zm;
+        const Vec<3> t = safe_normalized(vcross(n, a));
+        const Vec<3> b = safe_normalized(vcross(n, t));
+        Vec<3> r;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            r[k] = t[k] * v[0] + b[k] * v[1] + n[k] * v[2];
+        return r;
+    }
+
+    template <int D>
+    struct Dims;
+    template <>
+    struct Dims<2>
+    {
+        static WOST_DEV float sphere_pdf() { return 1.0f / DM_2PI; }
+        static WOST_DEV float hemi_pdf() { return 1.0f / DM_PI; }
+        static WOST_DEV float sphere_measure() { return DM_2PI; }
+        static WOST_DEV float cond_pdf(float dirPdf, float r) { return dm_div(dirPdf, r); }
+        static WOST_DEV float green_eval(float R, float r) { return dm_div(dm_log(dm_div(R, r)), DM_2PI); } // util/green.h:25-28
+        static WOST_DEV float green_norm(float R) { return dm_div(R * R, 4.0f); }
+    };
+    template <>
+    struct Dims<3>
+    {
+        static WOST_DEV float sphere_pdf() { return 1.0f / DM_4PI; }
+        static WOST_DEV float hemi_pdf() { return 1.0f / DM_2PI; }
+        static WOST_DEV float sphere_measure() { return DM_4PI; }
+        static WOST_DEV float cond_pdf(float dirPdf, float r) { return dm_div(dirPdf, r * r); }
+        static WOST_DEV float green_eval(float R, float r) { return dm_div(dm_div(1.0f, r) - dm_div(1.0f, R), DM_4PI); } // util/green.h:84-91
+        static WOST_DEV float green_norm(float R) { return dm_div(R * R, 6.0f); }
+    };
+
+    // util/green.h:45-74 (2D, bounded rejection) / :98-113 (3D, closed form)
+    WOST_DEV float green_sample_radius(float R, uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t depth, const Philox4 &, Vec<2> *)
+    {
+        const float bound = dm_div(1.5f, R);
+        float r = 0.0f;
+        int iter = 0;
+        do
+        {
+            const Philox4 q = wost_rng(seed, pixel, sample, depth, WOST_RNG_SOURCE_RAD, (uint32_t)iter);
+            const float u = u32_to_unit_float(q.x);
+            r = u32_to_unit_float(q.y) * R;
+            const float pdf = dm_div(Dims<2>::green_eval(R, r), Dims<2>::green_norm(R));
+            const float pdfRadius = dm_div(pdf, Dims<2>::sphere_pdf());
+            ++iter;
+            if (u < dm_div(pdfRadius, bound))
+                break;
+        } while (iter < 1000);
+        r = dm_max(1e-4f, r);
+        if (r > R)
+            r = dm_div(R, 2.0f);
+        return r;
+    }
+    WOST_DEV float green_sample_radius(float R, uint32_t, uint32_t, uint32_t, uint32_t, const Philox4 &dirdraw, Vec<3> *)
+    {
+        const float u1 = u32_to_unit_float(dirdraw.z), u2 = u32_to_unit_float(dirdraw.w);
+        const float phi = DM_2PI * u2;
+        float r = dm_div((1.0f + dm_sqrt(1.0f - dm_cbrt(u1 * u1)) * dm_cos(phi)) * R, 2.0f);
+        r = dm_max(1e-4f, r);
+        if (r > R)
+            r = dm_div(R, 2.0f);
+        return r;
+    }
+
+    // dense Vec3f grid, trilinear like NanoVDB SampleFromVoxels<Tree,1,false> (SampleFromVoxels.h:202-243,413-419)
+    template <int D>
+    WOST_DEV void source_lookup(const WalkCtx<D> &c, const float w3[3], float out[3])
+    {
+        float f[3];
+        int ijk[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+        {
+            const float x = (w3[k] - c.source_origin[k]) * c.source_inv_voxel;
+            const float fl = floorf(x);
+            ijk[k] = (int)fl;
+            f[k] = x - fl;
+        }
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch)
+        {
+            float v[2][2][2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int d = 0; d < 2; ++d)
+                    {
+                        const int i = ijk[0] + a, j = ijk[1] + b, k = ijk[2] + d;
+                        const bool in = i >= 0 && j >= 0 && k >= 0 && i < c.source_dims[0] && j < c.source_dims[1] && k < c.source_dims[2];
+                        v[a][b][d] = in ? __ldg(c.source + (((size_t)k * c.source_dims[1] + j) * c.source_dims[0] + i) * 3 + ch) : 0.0f;
+                    }
+            const float z00 = v[0][0][0] + f[2] * (v[0][0][1] - v[0][0][0]);
+            const float z01 = v[0][1][0] + f[2] * (v[0][1][1] - v[0][1][0]);
+            const float z10 = v[1][0][0] + f[2] * (v[1][0][1] - v[1][0][0]);
+            const float z11 = v[1][1][0] + f[2] * (v[1][1][1] - v[1][1][0]);
+            const float y0 = z00 + f[1] * (z01 - z00);
+            const float y1 = z10 + f[1] * (z11 - z10);
+            out[ch] = y0 + f[0] * (y1 - y0);
+        }
+    }
+
+    // Pixel accumulator handled like the reference's addColor (integrator/uniform/workqueue.h:25-29):
+    // loaded on first use, every contribution applied in stage order, stored once at the end of the step.
+    struct PixelAcc
+    {
+        float *ptr;
+        float v[3];
+        bool loaded;
+        WOST_DEV void init(float *p)
+        {
+            ptr = p;
+            loaded = false;
+        }
+        WOST_DEV void add(float c0, float c1, float c2)
+        {
+            if (!loaded)
+            {
+                v[0] = ptr[0];
+                v[1] = ptr[1];
+                v[2] = ptr[2];
+                loaded = true;
+            }
+            v[0] = c0 + v[0];
+            v[1] = c1 + v[1];
+            v[2] = c2 + v[2];
+        }
+        WOST_DEV void flush()
+        {
+            if (loaded)
+            {
+                ptr[0] = v[0];
+                ptr[1] = v[1];
+                ptr[2] = v[2];
+            }
+        }
+    };
+
+    // ---------------------------------------------------------------------------------------------------------
+    // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
+    template <int D>
+    WOST_DEV bool walk_step_uniform(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc)
+    {
+        const float eps = c.eps;
+        // ---- separate (integrator/uniform/integrator.cu:102-212)
+        float R_D = dm_inf();
+        if (c.dir.nprims > 0)
+        {
+            uint32_t pos;
+            query_nearest(c.dir, w.x, st, pos, R_D);
+            if (R_D < eps)
+            {
+                const Prim<D> pr = load_prim(c.dir.leaf_prim + pos);
+                float uv[2];
+                proj_ratio(pr, w.x, uv);
+                if (uv_strictly_inside<D>(uv))
+                {
+                    // ---- boundary (integrator.cu:214-232)
+                    const int side = point_side(pr, w.x);
+                    const uint32_t obj = __ldg(c.dir.leaf_obj + pos);
+                    int vidx[D];
+#pragma unroll
+                    for (int k = 0; k < D; ++k)
+                        vidx[k] = __ldg(c.dir_prims + (size_t)obj * D + k);
+                    float col[3];
+                    surface_color<D>(c.color_dir, vidx, side, uv, col);
+                    acc.add(col[0] * c.dirichlet_intensity * w.thp, col[1] * c.dirichlet_intensity * w.thp, col[2] * c.dirichlet_intensity * w.thp);
+                    return false;
+                }
+            }
+        }
+        float R_N = dm_inf();
+        if (c.neu.nprims > 0)
+            R_N = query_silhouette(c.neu, w.x, false, st);
+        float R_B = dm_fmax(1e-4f, dm_fmin(R_D, R_N));
+        R_B *= 0.99f;
+        if (dm_isinf(R_B))
+            return false;
+
+        // ---- source sample (integrator.cu:234-316)
+        if (c.source)
+        {
+            const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_SOURCE_DIR, 0);
+            Vec<D> dir;
+            float dirPdf, alpha = 1.0f;
+            if (w.onN)
+            {
+                dir = to_world(w.nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
+                dirPdf = Dims<D>::hemi_pdf();
+                alpha = 0.5f;
+            }
+            else
+            {
+                dir = sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
+                dirPdf = Dims<D>::sphere_pdf();
+            }
+            float dist = R_B;
+            if (c.neu.nprims > 0)
+            {
+                Vec<D> o;
+#pragma unroll
+                for (int k = 0; k < D; ++k)
+                    o[k] = w.x[k] + eps * dir[k];
+                const RayResult rr = query_ray<D, false>(c.neu, Ray<D>(o, dir), dist, st);
+                if (rr.hit)
+                    dist = dm_fmin(rr.t, dist);
+            }
+            const float r = green_sample_radius(R_B, c.seed, w.pixel, w.sample, depth, q, (Vec<D> *)nullptr);
+            if (r <= dist)
+            {
+                float w3[3];
+                w3[0] = w.x[0] + r * dir[0];
+                w3[1] = w.x[1] + r * dir[1];
+                w3[2] = (D == 3) ? w.x[D - 1] + r * dir[D - 1] : 0.0f;
+                float g[3];
+                source_lookup(c, w3, g);
+                float cc[3];
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch)
+                {
+                    const float gv = g[ch] * c.source_intensity;
+                    cc[ch] = dm_div(dm_div(w.thp * gv * Dims<D>::green_norm(R_B) * Dims<D>::cond_pdf(Dims<D>::sphere_pdf(), r), Dims<D>::cond_pdf(dirPdf, r)), alpha);
+                }
+                acc.add(cc[0], cc[1], cc[2]);
+            }
+        }
+
+        // ---- Neumann boundary sample (integrator.cu:318-445). Skipped when every Neumann colour is zero:
+        // the stage could then only add -0 to the pixel ("pure overhead there").
+        if (c.neu.nprims > 0 && c.neumann_flux_enabled)
+        {
+            const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_NEUMANN, 0);
+            const float u0 = u32_to_unit_float(q.x), u1 = u32_to_unit_float(q.y), u2 = u32_to_unit_float(q.z);
+            int pos;
+            float pdf;
+            sample_in_sphere(c.neu, w.x, R_B, u0, pos, pdf);
+            if (pos != -1 && pdf > 0)
+            {
+                const Prim<D> pr = load_prim(c.neu.leaf_prim + pos);
+                const Vec<D> y = sample_on_prim(pr, u1, u2);
+                const float r = vlen(vsub(y, w.x));
+                if (r < R_B && r > 0)
+                {
+                    Vec<D> o = w.x;
+                    if (w.onN)
+                    {
+#pragma unroll
+                        for (int k = 0; k < D; ++k)
+                            o[k] = o[k] + eps * w.nN[k];
+                    }
+                    Vec<D> rd = vsub(y, o);
+                    const float cl = vlen(rd);
+                    if (cl > 0)
+                    {
+#pragma unroll
+                        for (int k = 0; k < D; ++k)
+                            rd[k] = dm_div(rd[k], cl);
+                    }
+                    const bool blocked = query_ray<D, true>(c.neu, Ray<D>(o, rd), cl - eps, st).hit;
+                    if (!blocked)
+                    {
+                        int side = point_side(pr, w.x);
+                        float uv[2];
+                        proj_ratio(pr, y, uv);
+                        if (w.onN)
+                        {
+                            const float dn = vdot(prim_normal(pr), w.nN);
+                            side = (0.0f < dn) - (dn < 0.0f);
+                        }
+                        if (side != 0)
+                        {
+                            const uint32_t obj = __ldg(c.neu.leaf_obj + pos);
+                            int vidx[D];
+#pragma unroll
+                            for (int k = 0; k < D; ++k)
+                                vidx[k] = __ldg(c.neu_prims + (size_t)obj * D + k);
+                            float col[3];
+                            surface_color<D>(c.color_neu, vidx, side, uv, col);
+                            const float alpha = w.onN ? 0.5f : 1.0f;
+                            const float kf = dm_div(dm_div(w.thp * Dims<D>::green_eval(R_B, r), alpha), pdf);
+                            acc.add(-(col[0] * c.neumann_intensity * kf), -(col[1] * c.neumann_intensity * kf), -(col[2] * c.neumann_intensity * kf));
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- one-step walk (integrator.cu:447-526)
+        {
+            const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_WALK, 0);
+            Vec<D> cur = w.x, dir;
+            float pdf, alpha = 1.0f;
+            if (w.onN)
+            {
+                dir = to_world(w.nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
+                pdf = Dims<D>::hemi_pdf();
+                alpha = 0.5f;
+#pragma unroll
+                for (int k = 0; k < D; ++k)
+                    cur[k] = cur[k] + eps * w.nN[k];
+            }
+            else
+            {
+                dir = sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
+                pdf = Dims<D>::sphere_pdf();
+            }
+            Vec<D> next, normal;
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+            {
+                next[k] = w.x[k] + R_B * dir[k];
+                normal[k] = 0.0f;
+            }
+            bool hit = false;
+            if (c.neu.nprims > 0)
+            {
+                const RayResult rr = query_ray<D, false>(c.neu, Ray<D>(cur, dir), R_B, st);
+                hit = rr.hit;
+                if (hit)
+                {
+                    normal = prim_normal(load_prim(c.neu.leaf_prim + rr.leaf_pos));
+                    if (vdot(normal, dir) > 0)
+                    {
+#pragma unroll
+                        for (int k = 0; k < D; ++k)
+                            normal[k] = -normal[k];
+                    }
+#pragma unroll
+                    for (int k = 0; k < D; ++k)
+                        next[k] = cur[k] + rr.t * dir[k];
+                }
+            }
+            w.x = next;
+            w.thp = dm_div(dm_div(dm_div(w.thp, pdf), alpha), Dims<D>::sphere_measure());
+            w.onN = hit;
+            w.nN = normal;
+        }
+        return true;
+    }
+} // namespace wost

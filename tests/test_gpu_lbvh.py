@@ -1,0 +1,124 @@
+"""GPU: LBVH build + queries through the C ABI, bit-exact against the oracle and the reference's golden vectors."""
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_SCENES
+from helpers import bits, random_queries
+
+pytestmark = pytest.mark.gpu
+
+
+def _api():
+    from elaina_b200 import api
+    return api
+
+
+@pytest.mark.parametrize("name", GOLDEN_SCENES)
+def test_gpu_matches_reference_golden(golden, name):
+    api = _api()
+    g = {k.split("/", 1)[1]: golden[k] for k in golden.files if k.startswith(name + "/")}
+    dim = int(g["dim"])
+    s = api.Scene(dim, g["verts"], g["prims"])
+    nodes, aabbs, cones = s.dump_bvh()
+    assert np.array_equal(nodes, g["nodes"])
+    assert np.array_equal(bits(aabbs), bits(g["aabbs"]))
+    idx, dist = s.nearest(g["q"])
+    assert np.array_equal(idx, g["idx"])
+    assert np.array_equal(bits(dist), bits(g["dist"]))
+    assert np.array_equal(bits(s.silhouette(g["q"], False)), bits(g["sil0"]))
+    assert np.array_equal(bits(s.silhouette(g["q"], True)), bits(g["sil1"]))
+    hit, t, uv, obj = s.ray(g["q"], g["dir"], g["max_dist"])
+    assert np.array_equal(hit, g["hit"]) and np.array_equal(obj, g["obj"])
+    assert np.array_equal(bits(t), bits(g["t"])) and np.array_equal(bits(uv), bits(g["uv"]))
+    assert np.array_equal(s.ray_any(g["q"], g["dir"], g["max_dist"]), g["any"])
+    sobj, spdf = s.sample_in_sphere(g["q"], g["rad"], g["u"])
+    assert np.array_equal(sobj, g["sobj"])
+    np.testing.assert_allclose(spdf, g["spdf"], rtol=2e-5)
+
+
+def _scene_cases():
+    from elaina_b200 import scenes
+    cases = {}
+    cases["star10k"] = (2,) + scenes.star_polygon(10000)
+    cases["ico5"] = (3,) + scenes.icosphere(5, 1.0, 0.2)
+    rng = np.random.RandomState(9)
+    pts = rng.rand(3000, 2).astype(np.float32)
+    idx = rng.randint(0, 3000, (5000, 2)).astype(np.int32)
+    idx = idx[idx[:, 0] != idx[:, 1]]
+    cases["soup2d_random"] = (2, pts, idx)
+    tri = rng.rand(2000, 3).astype(np.float32)
+    tidx = rng.randint(0, 2000, (3000, 3)).astype(np.int32)
+    tidx = tidx[(tidx[:, 0] != tidx[:, 1]) & (tidx[:, 1] != tidx[:, 2]) & (tidx[:, 0] != tidx[:, 2])]
+    cases["soup3d_random"] = (3, tri, tidx)
+    cases["single_segment"] = (2, np.array([[0, 0], [1, 0.5]], np.float32), np.array([[0, 1]], np.int32))
+    cases["two_triangles"] = (3, np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 1, 0.3]], np.float32), np.array([[0, 1, 2], [1, 3, 2]], np.int32))
+    return cases
+
+
+@pytest.mark.parametrize("name", ["star10k", "ico5", "soup2d_random", "soup3d_random", "single_segment", "two_triangles"])
+def test_gpu_matches_oracle_bit_exact(oracle, name):
+    """Build order, topology, boxes AND cones bit-exact (one arithmetic), all five query kinds bit-exact."""
+    api = _api()
+    dim, v, p = _scene_cases()[name]
+    so = oracle.scene(dim, v, p)
+    sg = api.Scene(dim, v, p)
+    no, ao, co = so.dump_bvh()
+    ng, ag, cg = sg.dump_bvh()
+    assert np.array_equal(no, ng)
+    assert np.array_equal(bits(ao), bits(ag))
+    valid = co[:, dim] >= 0
+    assert np.array_equal(co[:, dim] < 0, cg[:, dim] < 0)
+    assert np.array_equal(bits(co[valid]), bits(cg[valid]))
+    mo, oo = oracle.dump_sorted(so)
+    mg, og = sg.dump_sorted()
+    assert np.array_equal(mo, mg) and np.array_equal(oo, og)
+    assert oracle.used_morton64(so) == sg.used_morton64
+    q, d, md, u, rad = random_queries(v, 20000, 4)
+    io, do = so.nearest(q)
+    ig, dg = sg.nearest(q)
+    assert np.array_equal(io, ig) and np.array_equal(bits(do), bits(dg))
+    for flip in (False, True):
+        assert np.array_equal(bits(so.silhouette(q, flip)), bits(sg.silhouette(q, flip)))
+    ho, to, uo, bo = so.ray(q, d, md)
+    hg, tg, ug, bg = sg.ray(q, d, md)
+    assert np.array_equal(ho, hg) and np.array_equal(bo, bg)
+    assert np.array_equal(bits(to), bits(tg)) and np.array_equal(bits(uo), bits(ug))
+    assert np.array_equal(so.ray_any(q, d, md), sg.ray_any(q, d, md))
+    po, fo = so.sample_in_sphere(q, rad, u)
+    pg, fg = sg.sample_in_sphere(q, rad, u)
+    assert np.array_equal(po, pg) and np.array_equal(bits(fo), bits(fg))
+
+
+def test_empty_and_invalid_inputs():
+    api = _api()
+    from elaina_b200._lib import WostError
+    v = np.array([[0, 0], [1, 0]], np.float32)
+    s = api.Scene(2, v, np.array([[0, 1]], np.int32))
+    idx, dist = s.nearest(np.zeros((0, 2), np.float32))
+    assert len(idx) == 0
+    with pytest.raises(WostError):
+        api.Scene(2, v, np.array([[0, 5]], np.int32))  # index out of range
+
+
+def test_full_size_query_properties():
+    """BASELINE-size check by properties: 1024^2 closest-point queries on a 10k-segment polygon.
+    d(x) is 1-Lipschitz, d == 0 on the vertices, and idx reproduces d by direct evaluation."""
+    api = _api()
+    from elaina_b200 import scenes
+    v, p = scenes.star_polygon(10000)
+    s = api.Scene(2, v, p)
+    g = np.linspace(-1.5, 1.5, 1024, dtype=np.float32)
+    X, Y = np.meshgrid(g, g)
+    q = np.stack([X.ravel(), Y.ravel()], 1)
+    idx, dist = s.nearest(q)
+    D = dist.reshape(1024, 1024)
+    h = g[1] - g[0]
+    assert np.all(np.abs(np.diff(D, axis=0)) <= h * 1.0001 + 1e-6)
+    assert np.all(np.abs(np.diff(D, axis=1)) <= h * 1.0001 + 1e-6)
+    a, b = v[p[idx, 0]].astype(np.float64), v[p[idx, 1]].astype(np.float64)
+    ab = b - a
+    t = np.clip(((q - a) * ab).sum(1) / (ab * ab).sum(1), 0, 1)
+    direct = np.linalg.norm(q - (a + t[:, None] * ab), axis=1)
+    np.testing.assert_allclose(dist, direct, rtol=1e-4, atol=1e-6)
+    _, dv = s.nearest(v)
+    assert np.all(dv <= 1e-6)
