@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""bench.py -- walk-steps/sec of the WoSt walker hot path (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3|c3-small|c4] [--impl ours|reference]
+
+One "step" = one solve() of the workload (all pixels x all samples-per-pixel x all bounces) -- the call
+UniformIntegrator::solve() of the reference (integrator/uniform/integrator.cu:666-672).
+  value     walk-steps/s, device-timed (CUDA events on the integrator's stream inside wost_solve, max over ranks),
+            scene/BVH/colours already resident in HBM.
+  e2e       the same metric through the C ABI from HOST buffers, per step: wost_scene_create (H2D of vertices and
+            primitives + LBVH build) -> wost_problem_create (H2D colours) -> wost_integrator_create -> wost_solve ->
+            wost_film_download (D2H), timed by wall clock around the whole sequence (max over ranks).
+  roofline  algorithmic bytes per walk-step x walk-steps / summed device time of the
+            fused walk-step kernel launches, against MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline  the scalar oracle (oracle/libwost_oracle.so, TEST INFRASTRUCTURE) timed on the host cores on a bounded
+            sample of the same workload (a band of pixel rows at reduced spp).
+Multi-GPU: evaluation points shard by interleaved row tiles; no data-path collective; the final film is
+summed over ranks with one NCCL all-reduce (outside the device-timed region, inside e2e).
+--impl reference: the reference has no CPU implementation of the walker (CUDA-only) and its CUDA build is
+unbuildable offline; per the tier rules this arm times the CPU oracle port with all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+
+METRIC = "walk_steps_per_sec"
+UNIT = "walk-steps/s"
+
+# algorithmic bytes per walk-step (DESIGN.md "Roofline"): state in/out + one root->leaf descent per query
+BYTES_PER_STEP = {"c3": 938, "c3-small": 938, "c4": 1910, "c1": 1850}
+
+
+def workload(name):
+    """-> dict(spec for Problem, settings kwargs, description). Synthetic scenes of BASELINE.json's named shapes."""
+    from elaina_b200 import scenes
+    if name in ("c3", "c3-small"):
+        # configs[2]: synthetic 2D Laplace, 10k-segment polygon, analytic harmonic solution Re(z^3), 1024^2, 256 spp
+        nseg = 10000
+        dv, dp = scenes.star_polygon(nseg)
+        W = 1024 if name == "c3" else 256
+        spp = 256 if name == "c3" else 16
+        diag = float(np.linalg.norm(np.array([3.0, 3.0])))
+        # evaluate the interior problem only (that is where Re(z^3) is the solution): mask = pixels inside the curve
+        g = 1.5 * (2.0 * np.arange(W, dtype=np.float64) / W - 1.0)
+        X, Y = np.meshgrid(g, g)
+        mask = (np.hypot(X, Y) < 1.0 + 0.3 * np.sin(5.0 * np.arctan2(Y, X)) - 4e-3).astype(np.uint8)
+        return dict(dim=2, dverts=dv, dprims=dp, nverts=None, nprims=None, mask=mask,
+                    color_dirichlet=scenes.gray_pairs(scenes.harmonic_2d(dv, 3)), color_neumann=None,
+                    grid_scale=1.5, grid_pos=(0.0, 0.0), grid_up=(0.0, 1.0), aabb_min=(-1.5, -1.5), aabb_max=(1.5, 1.5),
+                    frame=(W, W), depth=64, spp=spp, eps=1e-3 * diag, seed=42,
+                    desc="synthetic 2D Laplace, %d-segment star polygon, g=Re(z^3), %dx%d grid masked to the interior (%d active pixels), %d spp, depth 64" % (nseg, W, W, int(mask.sum()), spp))
+    if name == "c4":
+        # configs[3] shape at single-GPU bench scale: 3D Poisson on a displaced icosphere (uniform integrator)
+        dv, dp = scenes.icosphere(7, 1.0, 0.1)  # 327,680 triangles
+        src = np.ones((16, 16, 16, 3), np.float32)
+        return dict(dim=3, dverts=dv, dprims=dp, nverts=None, nprims=None,
+                    color_dirichlet=scenes.gray_pairs(scenes.harmonic_3d(dv)), color_neumann=None,
+                    source=src, source_origin=(-1.6, -1.6, -1.6), source_voxel=0.2,
+                    grid_scale=1.0, grid_pos=(0.0, 0.0, 0.0), grid_up=(0.0, 1.0, 0.0), grid_right=(1.0, 0.0, 0.0),
+                    aabb_min=(-1.5, -1.5, -1.5), aabb_max=(1.5, 1.5, 1.5),
+                    frame=(512, 512), depth=64, spp=64, eps=2e-3, seed=42,
+                    desc="synthetic 3D Poisson, 327,680-triangle displaced icosphere, 512x512 slice, 64 spp, depth 64")
+    raise SystemExit("unknown workload " + name)
+
+
+def problem_kwargs(wl):
+    keys = ("color_dirichlet", "color_neumann", "mask", "source", "source_origin", "source_voxel", "grid_scale", "grid_pos", "grid_up",
+            "grid_right", "aabb_min", "aabb_max")
+    return {k: wl[k] for k in keys if wl.get(k) is not None}
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md 'clocks' line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            try:
+                self.proc.terminate()
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_oracle_sample(wl, budget_s=12.0, nthreads=0):
+    """Time the scalar oracle on a bounded sample of the workload: rows around the frame centre, spp reduced."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle_lib import Oracle
+    orc = Oracle()
+    orc.set_math_mode(0)
+    dim = wl["dim"]
+    prob = dict(dim=dim, dirichlet=orc.scene(dim, wl["dverts"], wl["dprims"]),
+                neumann=orc.scene(dim, wl["nverts"], wl["nprims"]) if wl.get("nverts") is not None else None, **problem_kwargs(wl))
+    W, H = wl["frame"]
+    cores = nthreads if nthreads > 0 else (os.cpu_count() or 1)
+    st = dict(frame_w=W, frame_h=H, max_walking_depth=wl["depth"], samples_per_pixel=1, epsilon_shell=wl["eps"], seed=wl["seed"])
+    rows = 2
+    total_steps, total_t = 0, 0.0
+    r0 = H // 2
+    # grow the sample until ~budget_s of CPU work has been timed
+    while total_t < budget_s and r0 + rows <= H:
+        t0 = time.perf_counter()
+        _, steps = orc.solve_uniform(prob, st, pixel_begin=r0 * W, pixel_end=(r0 + rows) * W, nthreads=cores)
+        dt = time.perf_counter() - t0
+        total_steps += steps
+        total_t += dt
+        r0 += rows
+        if dt < budget_s / 8:
+            rows = min(rows * 2, H - r0) if H - r0 > 0 else rows
+        if rows <= 0:
+            break
+    sample = "%d pixel rows of the %dx%d frame from row %d, 1 spp, depth %d (%d walk-steps)" % (r0 - H // 2, W, H, H // 2, wl["depth"], total_steps)
+    return total_steps / max(total_t, 1e-9), cores, sample, total_steps, total_t
+
+
+def run_reference_arm(args, wl, rank, world):
+    if rank != 0:
+        return
+    vals = []
+    sample = ""
+    cores = os.cpu_count() or 1
+    for i in range(args.warmup + args.steps):
+        v, cores, sample, steps, t = cpu_oracle_sample(wl, budget_s=max(2.0, 60.0 / max(1, args.warmup + args.steps)))
+        if i >= args.warmup:
+            vals.append((steps, t))
+    steps = sum(s for s, _ in vals)
+    t = sum(t for _, t in vals)
+    value = steps / max(t, 1e-9)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": wl["desc"], "note": "reference walker is CUDA-only and unbuildable offline; CPU oracle port timed (DESIGN.md)"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": "per step: " + sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3")
+    ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (reported in config)")
+    ap.add_argument("--spp-batch", type=int, default=0)
+    ap.add_argument("--walk-mode", default="wavefront", choices=["wavefront", "reforder"],
+                    help="reforder: closest-point queries in the reference's visit order (stand-in for the reference's traversal cost)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg (line carries e2e: null)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = workload(args.workload)
+    if args.spp > 0:
+        wl["desc"] = wl["desc"].replace("%d spp" % wl["spp"], "%d spp" % args.spp)
+        wl["spp"] = args.spp
+    if args.impl == "reference":
+        run_reference_arm(args, wl, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from elaina_b200 import api
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA GPU (there is no CPU fallback for the walker)")
+    torch.cuda.set_device(local_rank)
+    api.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    dim = wl["dim"]
+    W, H = wl["frame"]
+    # strong scaling: the frame is fixed, rows are dealt to ranks in interleaved tiles of 4 rows (pixel-keyed RNG ->
+    # the summed film does not depend on N)
+    shard = dict(pixel_stride_rows=4, num_shards=world, shard=rank) if world > 1 else {}
+    settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=args.spp_batch, walk_mode=2 if args.walk_mode == "reforder" else 0, **shard)
+
+    def make_problem():
+        g_d = api.Scene(dim, wl["dverts"], wl["dprims"])
+        g_n = api.Scene(dim, wl["nverts"], wl["nprims"]) if wl.get("nverts") is not None else None
+        return api.Problem(dim, dirichlet=g_d, neumann=g_n, **problem_kwargs(wl))
+
+    prob = make_problem()
+    it = api.UniformIntegrator(prob, settings)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    film_t = None
+    if world > 1:
+        film_t = torch.empty(H * W * 5, dtype=torch.float32, device=dev)
+
+    # ---- device-timed: K solves, scene resident
+    for _ in range(args.warmup):
+        it.solve()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    dev_ms, steps_total, launches, kern_ms, kern_launches = 0.0, 0, 0, 0.0, 0
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        it.solve()
+        dev_ms += it.last_device_ms
+        steps_total += it.last_walk_steps
+        launches += it.launch_count
+        n, ms = it.step_kernel_time
+        kern_launches += n
+        kern_ms += ms
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = max_over_ranks(dev_ms)
+    kern_ms_max = max_over_ranks(kern_ms)
+    steps_all = sum_over_ranks(float(steps_total))
+    value = steps_all / (dev_ms * 1e-3)
+
+    # ---- end to end through the C ABI from host buffers
+    h2d = wl["dverts"].nbytes + wl["dprims"].nbytes + (wl["color_dirichlet"].nbytes if wl.get("color_dirichlet") is not None else 0)
+    if wl.get("nverts") is not None:
+        h2d += wl["nverts"].nbytes + wl["nprims"].nbytes + (wl["color_neumann"].nbytes if wl.get("color_neumann") is not None else 0)
+    if wl.get("source") is not None:
+        h2d += wl["source"].nbytes
+    d2h = W * H * 5 * 4
+    e2e_steps = 0
+
+    def e2e_once():
+        p = make_problem()
+        i2 = api.UniformIntegrator(p, settings)
+        i2.solve()
+        if world > 1:
+            # final film gather: shards own disjoint rows and write zeros elsewhere -> one NCCL sum
+            ptr = i2.film_device_ptr()
+            film = _wrap_device_ptr(torch, ptr, H * W * 5, dev)
+            film_t.copy_(film)
+            dist.all_reduce(film_t)
+            out = film_t.cpu() if rank == 0 else None
+            torch.cuda.synchronize()
+        else:
+            out = i2.film()
+        s = i2.last_walk_steps
+        i2.close()
+        p.close()
+        return s, out
+
+    n_e2e = max(1, min(args.steps, 3))
+    e2e_value = None
+    if not args.no_e2e:
+        e2e_once()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            s, _ = e2e_once()
+            e2e_steps += s
+        barrier()
+        e2e_t = max_over_ranks(time.perf_counter() - t0)
+        e2e_value = sum_over_ranks(float(e2e_steps)) / e2e_t
+
+    peak, peak_src = measured_peak()
+    bps = BYTES_PER_STEP[args.workload]
+    achieved = steps_total * bps / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, cores, sample, _, _ = cpu_oracle_sample(wl)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": wl["desc"], "integrator": "uniform", "walk_mode": args.walk_mode, "spp_batch": args.spp_batch or "auto (~16M walks in flight)",
+                       "walk_steps_per_step": steps_all / args.steps, "sharding": "interleaved 4-row tiles over %d ranks" % world,
+                       "l2": "256 MiB flush between timed steps; live working set (queues + accumulators, >1 GB) exceeds the 126 MB L2"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e,
+                    "path": "wost_scene_create+LBVH build -> wost_problem_create -> wost_integrator_create -> wost_solve -> wost_film_download"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "k_step_uniform<%d>" % dim, "bytes_per_walk_step": bps, "launches": int(kern_launches),
+                         "avg_launch_ms": kern_ms / max(1, kern_launches), "kernel_share_of_step": kern_ms_max / dev_ms if dev_ms > 0 else None,
+                         "peak_source": peak_src},
+            "clocks": clocks,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _wrap_device_ptr(torch, ptr, n_floats, dev):
+    """A float32 torch view over a device pointer owned by libwost.so (for NCCL collectives issued from Python)."""
+    class _Holder:
+        pass
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(h, device=dev)
+
+
+if __name__ == "__main__":
+    main()

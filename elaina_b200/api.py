@@ -280,5 +280,13 @@ class _Integrator:
         return n.value
 
 
+    @property
+    def step_kernel_time(self):
+        """-> (launches of the fused walk-step kernel, their summed device ms) of the last solve"""
+        n, ms = c_u64(), c_float()
+        check(_lib.load().wost_last_step_kernel_time(self.h, ctypes.byref(n), ctypes.byref(ms)))
+        return n.value, ms.value
+
+
 class UniformIntegrator(_Integrator):
     kind = UNIFORM

@@ -152,21 +152,24 @@ namespace wost
 
     // ------------------------------------------------------------------ primitives
     // scene.cuh:176-201 / 230-255
+    // *_d2 variants return the dot product the reference feeds to sqrt (length()), so that callers can defer the sqrt.
     template <int D>
-    WOST_HOSTDEV float closest_point_segment(const Vec<D> &pa, const Vec<D> &pb, const Vec<D> &x, Vec<D> *pt)
+    WOST_HOSTDEV float vlen2(const Vec<D> &a) { return vdot(a, a); }
+    template <int D>
+    WOST_HOSTDEV float closest_point_segment_d2(const Vec<D> &pa, const Vec<D> &pb, const Vec<D> &x, Vec<D> *pt)
     {
         const Vec<D> u = vsub(pb, pa), v = vsub(x, pa);
         const float c1 = vdot(u, v);
         if (c1 <= 0.0f)
         {
             *pt = pa;
-            return vlen(vsub(x, pa));
+            return vlen2(vsub(x, pa));
         }
         const float c2 = vdot(u, u);
         if (c2 <= c1)
         {
             *pt = pb;
-            return vlen(vsub(x, pb));
+            return vlen2(vsub(x, pb));
         }
         const float t = dm_div(c1, c2);
         Vec<D> q;
@@ -174,51 +177,61 @@ namespace wost
         for (int k = 0; k < D; ++k)
             q[k] = pa[k] + u[k] * t;
         *pt = q;
-        return vlen(vsub(x, q));
+        return vlen2(vsub(x, q));
+    }
+    template <int D>
+    WOST_HOSTDEV float closest_point_segment(const Vec<D> &pa, const Vec<D> &pb, const Vec<D> &x, Vec<D> *pt)
+    {
+        return dm_sqrt(closest_point_segment_d2(pa, pb, x, pt));
     }
     // scene.cuh:34-110
-    WOST_HOSTDEV float closest_point_triangle(const Vec<3> &pa, const Vec<3> &pb, const Vec<3> &pc, const Vec<3> &x)
+    WOST_HOSTDEV float closest_point_triangle_d2(const Vec<3> &pa, const Vec<3> &pb, const Vec<3> &pc, const Vec<3> &x)
     {
         const Vec<3> ab = vsub(pb, pa), ac = vsub(pc, pa), ax = vsub(x, pa);
         const float d1 = vdot(ab, ax), d2 = vdot(ac, ax);
         if (d1 <= 0.0f && d2 <= 0.0f)
-            return vlen(vsub(x, pa));
+            return vlen2(vsub(x, pa));
         const Vec<3> bx = vsub(x, pb);
         const float d3 = vdot(ab, bx), d4 = vdot(ac, bx);
         if (d3 >= 0.0f && d4 <= d3)
-            return vlen(vsub(x, pb));
+            return vlen2(vsub(x, pb));
         const Vec<3> cx = vsub(x, pc);
         const float d5 = vdot(ab, cx), d6 = vdot(ac, cx);
         if (d6 >= 0.0f && d5 <= d6)
-            return vlen(vsub(x, pc));
+            return vlen2(vsub(x, pc));
         Vec<3> pt;
         const float vc = d1 * d4 - d3 * d2;
         if (vc <= 0.0f && d1 >= 0.0f && d3 <= 0.0f)
         {
             const float v = dm_div(d1, d1 - d3);
             pt[0] = pa[0] + ab[0] * v, pt[1] = pa[1] + ab[1] * v, pt[2] = pa[2] + ab[2] * v;
-            return vlen(vsub(x, pt));
+            return vlen2(vsub(x, pt));
         }
         const float vb = d5 * d2 - d1 * d6;
         if (vb <= 0.0f && d2 >= 0.0f && d6 <= 0.0f)
         {
             const float w = dm_div(d2, d2 - d6);
             pt[0] = pa[0] + ac[0] * w, pt[1] = pa[1] + ac[1] * w, pt[2] = pa[2] + ac[2] * w;
-            return vlen(vsub(x, pt));
+            return vlen2(vsub(x, pt));
         }
         const float va = d3 * d6 - d5 * d4;
         if (va <= 0.0f && (d4 - d3) >= 0.0f && (d5 - d6) >= 0.0f)
         {
             const float w = dm_div(d4 - d3, (d4 - d3) + (d5 - d6));
             pt[0] = pb[0] + (pc[0] - pb[0]) * w, pt[1] = pb[1] + (pc[1] - pb[1]) * w, pt[2] = pb[2] + (pc[2] - pb[2]) * w;
-            return vlen(vsub(x, pt));
+            return vlen2(vsub(x, pt));
         }
         const float denom = dm_div(1.0f, va + vb + vc);
         const float v = vb * denom, w = vc * denom;
         pt[0] = pa[0] + ab[0] * v + ac[0] * w;
         pt[1] = pa[1] + ab[1] * v + ac[1] * w;
         pt[2] = pa[2] + ab[2] * v + ac[2] * w;
-        return vlen(vsub(x, pt));
+        return vlen2(vsub(x, pt));
+    }
+
+    WOST_HOSTDEV float closest_point_triangle(const Vec<3> &pa, const Vec<3> &pb, const Vec<3> &pc, const Vec<3> &x)
+    {
+        return dm_sqrt(closest_point_triangle_d2(pa, pb, pc, x));
     }
 
     // Primitive with its vertices resolved (what a leaf stores inline)
@@ -235,6 +248,15 @@ namespace wost
     WOST_HOSTDEV float prim_distance(const Prim<3> &pr, const Vec<3> &x) // scene.cuh:963-976
     {
         return closest_point_triangle(pr.p[0], pr.p[1], pr.p[2], x);
+    }
+    WOST_HOSTDEV float prim_distance_d2(const Prim<2> &pr, const Vec<2> &x)
+    {
+        Vec<2> pt;
+        return closest_point_segment_d2(pr.p[0], pr.p[1], x, &pt);
+    }
+    WOST_HOSTDEV float prim_distance_d2(const Prim<3> &pr, const Vec<3> &x)
+    {
+        return closest_point_triangle_d2(pr.p[0], pr.p[1], pr.p[2], x);
     }
 
     // core/utility.cuh:569-635

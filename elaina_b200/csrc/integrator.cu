@@ -73,7 +73,7 @@ namespace wost
         int *overflow;
     };
 
-    template <int D, bool First>
+    template <int D, bool First, bool RefOrder>
     __global__ void __launch_bounds__(kWalkBlock) k_step_uniform(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ StepArgs a)
     {
         extern __shared__ uint2 smem_stack[];
@@ -112,7 +112,7 @@ namespace wost
                     load_item(a.in, (size_t)i, w);
                 PixelAcc acc;
                 acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
-                alive = walk_step_uniform<D>(c, w, a.depth, st, acc);
+                alive = walk_step_uniform<D, RefOrder>(c, w, a.depth, st, acc);
                 acc.flush();
             }
             if (!a.last_depth)
@@ -197,7 +197,7 @@ namespace wost
         }
     }
 
-    template <int D>
+    template <int D, bool RefOrder>
     static wost_status solve_uniform(wost_integrator *it, uint64_t *walk_steps)
     {
         WalkCtx<D> ctx;
@@ -213,18 +213,28 @@ namespace wost
         cudaStream_t st = it->stream;
         const size_t smem = stack_smem_bytes(kWalkBlock);
         int occ = 1;
-        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_step_uniform<D, false>, kWalkBlock, smem));
+        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_step_uniform<D, false, RefOrder>, kWalkBlock, smem));
         const int grid_full = sm_count() * std::max(1, occ);
 
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0;
+        it->step_launches = 0;
+        it->step_kernel_ms = 0.0f;
+        const int nbatches = it->n_active > 0 ? (spp + S - 1) / S : 0;
+        while ((int)it->batch_ev.size() < 2 * nbatches)
+        {
+            cudaEvent_t e;
+            WOST_CUDA_TRY(cudaEventCreate(&e));
+            it->batch_ev.push_back(e);
+        }
         if (it->n_active > 0)
         {
-            for (int s0 = 0; s0 < spp; s0 += S)
+            for (int s0 = 0, bi = 0; s0 < spp; s0 += S, ++bi)
             {
                 const int Sb = std::min(S, spp - s0);
                 WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int) * (size_t)(2 * (maxd + 1)), st));
+                WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi], st));
                 for (int depth = 0; depth < maxd; ++depth)
                 {
                     StepArgs a;
@@ -247,12 +257,14 @@ namespace wost
                     {
                         const long long n0 = (long long)it->n_active * Sb;
                         const int grid = (int)std::min<long long>(grid_full, (n0 + kWalkBlock - 1) / kWalkBlock);
-                        k_step_uniform<D, true><<<std::max(1, grid), kWalkBlock, smem, st>>>(ctx, a);
+                        k_step_uniform<D, true, RefOrder><<<std::max(1, grid), kWalkBlock, smem, st>>>(ctx, a);
                     }
                     else
-                        k_step_uniform<D, false><<<grid_full, kWalkBlock, smem, st>>>(ctx, a);
+                        k_step_uniform<D, false, RefOrder><<<grid_full, kWalkBlock, smem, st>>>(ctx, a);
                     ++it->launches;
+                    ++it->step_launches;
                 }
+                WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));
             }
         }
         k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
@@ -266,6 +278,12 @@ namespace wost
         WOST_CUDA_TRY(cudaStreamSynchronize(st));
         if (walk_steps)
             *walk_steps = h_steps;
+        for (int bi = 0; bi < nbatches; ++bi)
+        {
+            float f = 0.0f;
+            WOST_CUDA_TRY(cudaEventElapsedTime(&f, it->batch_ev[2 * bi], it->batch_ev[2 * bi + 1]));
+            it->step_kernel_ms += f;
+        }
         if (h_over)
         {
             cudaMemsetAsync(it->d_overflow.ptr, 0, sizeof(int), st);
@@ -466,7 +484,11 @@ extern "C"
             return WOST_ERR_INVALID;
         const auto t0 = std::chrono::high_resolution_clock::now();
         WOST_CUDA_TRY(cudaEventRecord(it->ev0, it->stream));
-        wost_status rc = (it->dim == 2) ? solve_uniform<2>(it, walk_steps) : solve_uniform<3>(it, walk_steps);
+        wost_status rc;
+        if (it->s.walk_mode == WOST_MODE_REFERENCE_ORDER)
+            rc = (it->dim == 2) ? solve_uniform<2, true>(it, walk_steps) : solve_uniform<3, true>(it, walk_steps);
+        else
+            rc = (it->dim == 2) ? solve_uniform<2, false>(it, walk_steps) : solve_uniform<3, false>(it, walk_steps);
         if (rc != WOST_OK)
             return rc;
         const auto t1 = std::chrono::high_resolution_clock::now();
@@ -529,6 +551,14 @@ extern "C"
         if (!it || !kernel_launches)
             return WOST_ERR_INVALID;
         *kernel_launches = it->launches;
+        return WOST_OK;
+    }
+    wost_status wost_last_step_kernel_time(wost_integrator *it, uint64_t *step_launches, float *step_kernel_ms)
+    {
+        if (!it || !step_launches || !step_kernel_ms)
+            return WOST_ERR_INVALID;
+        *step_launches = it->step_launches;
+        *step_kernel_ms = it->step_kernel_ms;
         return WOST_OK;
     }
 }

@@ -38,9 +38,14 @@ struct wost_integrator
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     uint64_t launches = 0;
+    uint64_t step_launches = 0;  // launches of the fused walk-step kernel in the last solve
+    float step_kernel_ms = 0.0f; // device time between the first and last walk-step launch of every spp batch, summed
+    std::vector<cudaEvent_t> batch_ev; // 2 events per spp batch
 
     ~wost_integrator()
     {
+        for (cudaEvent_t e : batch_ev)
+            cudaEventDestroy(e);
         if (ev0)
             cudaEventDestroy(ev0);
         if (ev1)

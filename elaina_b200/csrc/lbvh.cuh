@@ -15,6 +15,9 @@
 
 namespace wost
 {
+    // The boxes inside TNode are the EXACT extents of the children (no padding). The reference's padded boxes are
+    // rebuilt per visit with one add per coordinate (pad_box): bit-identical to its leaf boxes and to its merged
+    // internal boxes because x -> fl(x + c) is monotone, so max_i fl(a_i + c) == fl(max_i a_i + c).
     template <int D>
     struct TNode; // nearest / ray / sphere-descent record
     template <>
@@ -90,6 +93,8 @@ namespace wost
         const CNode<D> *cnodes;     // nprims-1
         const LeafPrim<D> *leaf_prim; // nprims (Morton order)
         const uint32_t *leaf_obj;   // nprims: original object index of leaf position
+        const uint32_t *leaf_rank;  // nprims: visit rank of the leaf in the reference's closest-point order (tie-break)
+        float max_abs_coord;        // max |coordinate| of the mesh (rounding slack of the closest-point pruning)
         const LeafSil<D> *leaf_sil; // nprims*D
         float root_box[2 * D];      // up, lo
         float root_cone[D + 2];
@@ -101,29 +106,60 @@ namespace wost
     template <int D>
     struct NodeView
     {
-        Box<D> lb, rb;
+        Box<D> lb, rb; // the reference's (padded) boxes
         uint32_t lref, rref;
     };
-    WOST_DEV NodeView<2> load_tnode(const TNode<2> *n)
+    template <int D>
+    struct NodeViewE
+    {
+        Box<D> le, re; // exact extents
+        uint32_t lref, rref;
+    };
+    // scene.cuh:429-430 (2D: +-bvh_offset) / aabb.cuh:21-50,93-101 (3D: +-epsilon<float>())
+    template <int D>
+    WOST_DEV Box<D> pad_box(const Box<D> &e)
+    {
+        const float pad = (D == 2) ? kBvhOffset : kEps;
+        Box<D> b;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+        {
+            b.up[k] = e.up[k] + pad;
+            b.lo[k] = e.lo[k] - pad;
+        }
+        return b;
+    }
+    WOST_DEV NodeViewE<2> load_tnode_e(const TNode<2> *n)
     {
         const float4 a = ldg4(n), b = ldg4(reinterpret_cast<const char *>(n) + 16), c = ldg4(reinterpret_cast<const char *>(n) + 32);
-        NodeView<2> v;
-        v.lb.up[0] = a.x, v.lb.up[1] = a.y, v.lb.lo[0] = a.z, v.lb.lo[1] = a.w;
-        v.rb.up[0] = b.x, v.rb.up[1] = b.y, v.rb.lo[0] = b.z, v.rb.lo[1] = b.w;
+        NodeViewE<2> v;
+        v.le.up[0] = a.x, v.le.up[1] = a.y, v.le.lo[0] = a.z, v.le.lo[1] = a.w;
+        v.re.up[0] = b.x, v.re.up[1] = b.y, v.re.lo[0] = b.z, v.re.lo[1] = b.w;
         v.lref = __float_as_uint(c.x);
         v.rref = __float_as_uint(c.y);
         return v;
     }
-    WOST_DEV NodeView<3> load_tnode(const TNode<3> *n)
+    WOST_DEV NodeViewE<3> load_tnode_e(const TNode<3> *n)
     {
         const char *q = reinterpret_cast<const char *>(n);
         const float4 a = ldg4(q), b = ldg4(q + 16), c = ldg4(q + 32), d = ldg4(q + 48);
-        NodeView<3> v;
-        v.lb.up[0] = a.x, v.lb.up[1] = a.y, v.lb.up[2] = a.z, v.lb.lo[0] = a.w;
-        v.lb.lo[1] = b.x, v.lb.lo[2] = b.y, v.rb.up[0] = b.z, v.rb.up[1] = b.w;
-        v.rb.up[2] = c.x, v.rb.lo[0] = c.y, v.rb.lo[1] = c.z, v.rb.lo[2] = c.w;
+        NodeViewE<3> v;
+        v.le.up[0] = a.x, v.le.up[1] = a.y, v.le.up[2] = a.z, v.le.lo[0] = a.w;
+        v.le.lo[1] = b.x, v.le.lo[2] = b.y, v.re.up[0] = b.z, v.re.up[1] = b.w;
+        v.re.up[2] = c.x, v.re.lo[0] = c.y, v.re.lo[1] = c.z, v.re.lo[2] = c.w;
         v.lref = __float_as_uint(d.x);
         v.rref = __float_as_uint(d.y);
+        return v;
+    }
+    template <int D>
+    WOST_DEV NodeView<D> load_tnode(const TNode<D> *n)
+    {
+        const NodeViewE<D> e = load_tnode_e(n);
+        NodeView<D> v;
+        v.lb = pad_box(e.le);
+        v.rb = pad_box(e.re);
+        v.lref = e.lref;
+        v.rref = e.rref;
         return v;
     }
     WOST_DEV void load_cnode(const CNode<2> *n, Cone<2> &l, Cone<2> &r)
@@ -247,8 +283,12 @@ namespace wost
     // Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]) and the distance.
     // Visit order mirrors the reference: L handled before R, leaves evaluated immediately, internal children
     // pushed L then R (R popped first); "<=" keeps the last visited of exact ties.
-    template <int D>
-    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist)
+    // Restricted = true: additionally skip every child whose EXACT-extent mindist exceeds thrW. Used as the second pass
+    // of query_nearest: with thrW a little above the final minimum only the subtrees that can hold the (near-)tied
+    // minima are walked, in the reference's order and with the reference's own pop-time test on the padded mindist, so
+    // the winner among ties and near-ties is the reference's even where that depends on its visit order.
+    template <int D, bool Restricted>
+    WOST_DEV void query_nearest_ref_impl(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, float thrW, uint32_t &leaf_pos, float &dist)
     {
         leaf_pos = kInvalid;
         float best = dm_inf();
@@ -281,10 +321,16 @@ namespace wost
             have = false;
             if (node_d > best)
                 continue;
-            const NodeView<D> n = load_tnode(bvh.tnodes + node);
-            const float Lmin = box_mindist(n.lb, q), Rmin = box_mindist(n.rb, q);
-            const float Lmm = box_minmaxdist(n.lb, q), Rmm = box_minmaxdist(n.rb, q);
-            const bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
+            const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
+            const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
+            const float Lmin = box_mindist(lp, q), Rmin = box_mindist(rp, q);
+            const float Lmm = box_minmaxdist(lp, q), Rmm = box_minmaxdist(rp, q);
+            bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
+            if (Restricted)
+            {
+                goL = goL && box_mindist(n.le, q) <= thrW;
+                goR = goR && box_mindist(n.re, q) <= thrW;
+            }
             bool pushL = false;
             if (goL)
             {
@@ -333,6 +379,153 @@ namespace wost
                 node_d = Lmin;
                 have = true;
             }
+        }
+        dist = dm_sqrt(best);
+    }
+    template <int D>
+    WOST_DEV void query_nearest_ref(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist)
+    {
+        query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist);
+    }
+
+    // ---------------------------------------------------------------- closest primitive, B200 traversal order
+    // Same RESULT as query_nearest_ref (index and distance bit for bit), ~5x fewer node visits on curve-like meshes.
+    // Pass 1 finds the minimum with an order the reference does not use:
+    //   * the reference's sibling rule "mindist(child) <= minmaxdist(sibling)" (query.cuh:279,299) is evaluated on the
+    //     rebuilt padded boxes exactly as the reference does -- it is local to a node, hence independent of visit order,
+    //     and it defines the candidate set S of leaves the reference can ever reach;
+    //   * pruning by the running best is free to be aggressive: children are visited nearest first and a child is
+    //     dropped as soon as the mindist of its EXACT extent exceeds (sqrt(best) + slack)^2, also at leaf level (the
+    //     reference only tests at pop time, on padded boxes, in fixed L/R order). slack = 2^-19 * max |coordinate|
+    //     (>= 16 ulp) covers the rounding of the leaf distance itself, so no (near-)minimal leaf is dropped;
+    //   * the sqrt + re-square of the reference (dist = length(..); dist *= dist) is only done for leaves whose squared
+    //     length can still win (x -> fl(fl(sqrt x)^2) is monotone and within 3 ulp of x).
+    // Which leaf the reference returns among EXACT ties (shared vertices / edges):
+    //   * 2D (boxes padded by 1e-3, scene.cuh:12): the reference's pop-time test can never drop a tied minimum, so it
+    //     returns the last visited one of its static order == the highest leaf_rank. No second pass.
+    //   * 3D (boxes padded by one float epsilon, aabb.cuh:21-50): the pop-time test compares the padded mindist with
+    //     the re-squared best and drops tied / 1-ulp-near minima depending on visit order. Whenever pass 1 saw more than
+    //     one leaf within 8 ulp of the minimum, pass 2 re-walks just those subtrees in the reference's order
+    //     (query_nearest_ref_impl<Restricted>) and takes its answer.
+    //   * far field (|q| beyond ~1000x the mesh, where fp32 collapses all distances): the reference order itself.
+    template <int D>
+    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist)
+    {
+        leaf_pos = kInvalid;
+        float best = dm_inf(); // re-squared distance of the winner, as the reference keeps it
+        if (bvh.nprims <= 0)
+        {
+            dist = best;
+            return;
+        }
+        float qmax = 0.0f;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            qmax = fmax_nn(qmax, dm_abs(q[k]));
+        const bool far = qmax > 1024.0f * bvh.max_abs_coord || (D == 2 && qmax > 2000.0f);
+        if (bvh.nprims == 1 || far)
+        {
+            query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist);
+            return;
+        }
+        const float slack = fmax_nn(qmax, bvh.max_abs_coord) * 1.9073486328125e-06f; // 2^-19
+        float thr = dm_inf();                                                          // (sqrt(best) + slack)^2
+        uint32_t best_rank = 0;
+        bool have_rank = false;
+        int n_near = 0; // leaves seen within 8 ulp of the running minimum (3D tie detection)
+        st.sp = 0;
+        uint32_t node = 0;
+        for (;;)
+        {
+            const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
+            const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
+            const float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
+            bool goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
+            bool goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
+#pragma unroll
+            for (int side = 0; side < 2; ++side)
+            {
+                const uint32_t ref = side == 0 ? n.lref : n.rref;
+                const bool go = side == 0 ? goL : goR;
+                const float e = side == 0 ? Le : Re;
+                if (go && (ref & kLeafFlag) && e <= thr)
+                {
+                    const uint32_t pos = ref & ~kLeafFlag;
+                    const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
+                    if (d2 <= best * 1.000002f)
+                    {
+                        const float d = dm_sqrt(d2);
+                        const float g = d * d;
+                        bool take = g < best;
+                        if (D == 3)
+                        {
+                            if (take)
+                                n_near = (best <= g * 1.000001f) ? n_near + 1 : 1;
+                            else if (g <= best * 1.000001f)
+                                ++n_near;
+                        }
+                        if (take)
+                            have_rank = false;
+                        else if (D == 2 && g == best && leaf_pos != kInvalid)
+                        {
+                            // exact tie: the reference keeps the last visited leaf of its own (static) order
+                            const uint32_t rk = __ldg(bvh.leaf_rank + pos);
+                            if (!have_rank)
+                            {
+                                best_rank = __ldg(bvh.leaf_rank + leaf_pos);
+                                have_rank = true;
+                            }
+                            take = rk > best_rank;
+                            if (take)
+                                best_rank = rk;
+                        }
+                        if (take)
+                        {
+                            best = g;
+                            leaf_pos = pos;
+                            const float t = d + slack;
+                            thr = t * t;
+                        }
+                    }
+                }
+            }
+            goL = goL && !(n.lref & kLeafFlag) && Le <= thr;
+            goR = goR && !(n.rref & kLeafFlag) && Re <= thr;
+            if (goL && goR)
+            {
+                const bool lnear = Le <= Re;
+                st.push(lnear ? n.rref : n.lref, lnear ? Re : Le);
+                node = lnear ? n.lref : n.rref;
+                continue;
+            }
+            if (goL)
+            {
+                node = n.lref;
+                continue;
+            }
+            if (goR)
+            {
+                node = n.rref;
+                continue;
+            }
+            bool found = false;
+            while (!st.empty())
+            {
+                const StackEntry e = st.pop();
+                if (e.d <= thr)
+                {
+                    node = e.ref;
+                    found = true;
+                    break;
+                }
+            }
+            if (!found)
+                break;
+        }
+        if (D == 3 && n_near > 1)
+        {
+            query_nearest_ref_impl<D, true>(bvh, q, st, thr, leaf_pos, dist);
+            return;
         }
         dist = dm_sqrt(best);
     }

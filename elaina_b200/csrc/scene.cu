@@ -185,6 +185,30 @@ namespace wost
         return b;
     }
 
+    // exact (unpadded) extents: the reference's padded box is fl(extent +- pad) per coordinate, for leaves AND for
+    // merged internal boxes (max_i fl(a_i + c) == fl(max_i a_i + c)), so the traversal records store the exact extents
+    // and rebuild the padded box with one add per coordinate (lbvh.cuh: pad_box).
+    template <int D>
+    WOST_DEV Box<D> prim_extent(const float *verts, const int *prim)
+    {
+        Box<D> b;
+        const Vec<D> p0 = ld_vert<D>(verts, prim[0]);
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            b.up[k] = b.lo[k] = p0[k];
+        for (int v = 1; v < D; ++v)
+        {
+            const Vec<D> p = ld_vert<D>(verts, prim[v]);
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+            {
+                b.lo[k] = dm_fmin(b.lo[k], p[k]);
+                b.up[k] = dm_fmax(b.up[k], p[k]);
+            }
+        }
+        return b;
+    }
+
     // ------------------------------------------------------------------ build kernels
     // leaf boxes + cones in ORIGINAL primitive order (scene.cuh:435-502 / 887-961)
     template <int D>
@@ -359,7 +383,7 @@ namespace wost
     WOST_DEV int cub_bits(unsigned long long a, unsigned long long b) { return __clzll(a ^ b); }
     // core/bvh.cuh:110-229 (Karras 2012)
     template <typename U>
-    __global__ void k_karras(int n, const U *code, Node *nodes)
+    __global__ void k_karras(int n, const U *code, Node *nodes, int *leaf_count)
     {
         const int idx = blockIdx.x * blockDim.x + threadIdx.x;
         if (idx >= n - 1)
@@ -435,6 +459,7 @@ namespace wost
             L += n - 1;
         if (last == gamma + 1)
             R += n - 1;
+        leaf_count[idx] = last - first + 1;
         nodes[idx].left = L;
         nodes[idx].right = R;
         nodes[idx].object = kInvalid;
@@ -505,13 +530,51 @@ namespace wost
         }
     }
 
+    // exact extents of the leaves in sorted order (internal nodes: k_refit_boxes on this buffer)
+    template <int D>
+    __global__ void k_leaf_extents(int n, const uint32_t *order, const float *verts, const int *prims, float *ext)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n)
+            return;
+        st_box<D>(ext, (size_t)(n - 1) + i, prim_extent<D>(verts, prims + (size_t)order[i] * D));
+    }
+    // Visit rank of every leaf in the reference's closest-point traversal order (core/query.cuh:279-314): at a node the
+    // L leaf child is evaluated first, then the R leaf child, then the whole R subtree (pushed last, popped first), then
+    // the L subtree. Among exactly tied distances the reference keeps the LAST visited leaf ("<="), i.e. the one with the
+    // highest rank -- which lets query_nearest visit nodes in any order and still return the reference's index.
+    __global__ void k_leaf_rank(int n, const Node *nodes, const int *leaf_count, uint32_t *rank)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n)
+            return;
+        const uint32_t first_leaf = (uint32_t)(n - 1);
+        uint32_t child = first_leaf + i, r = 0;
+        uint32_t p = nodes[child].parent;
+        while (p != kInvalid)
+        {
+            const uint32_t L = nodes[p].left, R = nodes[p].right;
+            const bool Lleaf = L >= first_leaf, Rleaf = R >= first_leaf;
+            if (child == L)
+            {
+                if (!Lleaf)
+                    r += Rleaf ? 1u : (uint32_t)leaf_count[R];
+            }
+            else
+                r += Lleaf ? 1u : 0u;
+            child = p;
+            p = nodes[p].parent;
+        }
+        rank[i] = r;
+    }
+
     // ------------------------------------------------------------------ traversal layout
     WOST_DEV uint32_t child_ref(const Node *nodes, uint32_t child, int n)
     {
         return (nodes[child].object != kInvalid) ? ((child - (uint32_t)(n - 1)) | kLeafFlag) : child;
     }
     template <int D>
-    __global__ void k_layout_internal(int n, const Node *nodes, const float *boxes, const float *cones, TNode<D> *tn, CNode<D> *cn)
+    __global__ void k_layout_internal(int n, const Node *nodes, const float *ext, const float *cones, TNode<D> *tn, CNode<D> *cn)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x;
         if (i >= n - 1)
@@ -521,8 +584,8 @@ namespace wost
 #pragma unroll
         for (int k = 0; k < 2 * D; ++k)
         {
-            t.lb[k] = boxes[(size_t)l * 2 * D + k];
-            t.rb[k] = boxes[(size_t)r * 2 * D + k];
+            t.lb[k] = ext[(size_t)l * 2 * D + k];
+            t.rb[k] = ext[(size_t)r * 2 * D + k];
         }
         t.lref = child_ref(nodes, l, n);
         t.rref = child_ref(nodes, r, n);
@@ -717,7 +780,8 @@ namespace wost
         cudaStream_t st = 0;
         DevBuf<float> lboxes, lcones, partial;
         DevBuf<uint32_t> code_in, idx_in;
-        DevBuf<int> flags, dup;
+        DevBuf<int> flags, dup, leaf_count;
+        DevBuf<float> ext;
         DevBuf<unsigned long long> key64;
         DevBuf<char> temp;
         WOST_CUDA_TRY(lboxes.alloc((size_t)n * 2 * D));
@@ -730,6 +794,9 @@ namespace wost
         WOST_CUDA_TRY(s->d_boxes.alloc((size_t)NN * 2 * D));
         WOST_CUDA_TRY(s->d_cones.alloc((size_t)NN * (D + 2)));
         WOST_CUDA_TRY(flags.alloc(std::max(1, n - 1)));
+        WOST_CUDA_TRY(leaf_count.alloc(std::max(1, n - 1)));
+        WOST_CUDA_TRY(ext.alloc((size_t)NN * 2 * D));
+        WOST_CUDA_TRY(s->d_leaf_rank.alloc(n));
         WOST_CUDA_TRY(dup.alloc(1));
         WOST_CUDA_TRY(cudaMemsetAsync(dup.ptr, 0, sizeof(int), st));
 
@@ -759,15 +826,22 @@ namespace wost
             {
                 WOST_CUDA_TRY(key64.alloc(n));
                 k_keys64<<<div_up(n, B), B, 0, st>>>(n, s->d_morton.ptr, s->d_order.ptr, key64.ptr);
-                k_karras<unsigned long long><<<div_up(n - 1, B), B, 0, st>>>(n, key64.ptr, s->d_nodes.ptr);
+                k_karras<unsigned long long><<<div_up(n - 1, B), B, 0, st>>>(n, key64.ptr, s->d_nodes.ptr, leaf_count.ptr);
             }
             else
-                k_karras<uint32_t><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_morton.ptr, s->d_nodes.ptr);
+                k_karras<uint32_t><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_morton.ptr, s->d_nodes.ptr, leaf_count.ptr);
             WOST_CUDA_TRY(cudaMemsetAsync(flags.ptr, 0, sizeof(int) * (size_t)(n - 1), st));
             k_refit_boxes<D><<<div_up(n, B), B, 0, st>>>(n, s->d_nodes.ptr, s->d_boxes.ptr, flags.ptr);
             WOST_CUDA_TRY(cudaMemsetAsync(flags.ptr, 0, sizeof(int) * (size_t)(n - 1), st));
             k_refit_cones<D><<<div_up(n, B), B, 0, st>>>(n, s->d_nodes.ptr, s->d_boxes.ptr, s->d_cones.ptr, flags.ptr);
         }
+        k_leaf_extents<D><<<div_up(n, B), B, 0, st>>>(n, s->d_order.ptr, s->d_verts.ptr, s->d_prims.ptr, ext.ptr);
+        if (n > 1)
+        {
+            WOST_CUDA_TRY(cudaMemsetAsync(flags.ptr, 0, sizeof(int) * (size_t)(n - 1), st));
+            k_refit_boxes<D><<<div_up(n, B), B, 0, st>>>(n, s->d_nodes.ptr, ext.ptr, flags.ptr);
+        }
+        k_leaf_rank<<<div_up(n, B), B, 0, st>>>(n, s->d_nodes.ptr, leaf_count.ptr, s->d_leaf_rank.ptr);
         // traversal layout
         WOST_CUDA_TRY(s->d_tnodes.alloc(sizeof(TNode<D>) * (size_t)std::max(1, n - 1)));
         WOST_CUDA_TRY(s->d_cnodes.alloc(sizeof(CNode<D>) * (size_t)std::max(1, n - 1)));
@@ -775,13 +849,14 @@ namespace wost
         WOST_CUDA_TRY(s->d_leaf_sil.alloc(sizeof(LeafSil<D>) * (size_t)n * D));
         WOST_CUDA_TRY(s->d_leaf_obj.alloc(n));
         if (n > 1)
-            k_layout_internal<D><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_nodes.ptr, s->d_boxes.ptr, s->d_cones.ptr,
+            k_layout_internal<D><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_nodes.ptr, ext.ptr, s->d_cones.ptr,
                                                                   reinterpret_cast<TNode<D> *>(s->d_tnodes.ptr), reinterpret_cast<CNode<D> *>(s->d_cnodes.ptr));
         k_layout_leaves<D><<<div_up(n, B), B, 0, st>>>(n, s->d_order.ptr, s->d_verts.ptr, s->d_prims.ptr, s->d_sil_rec.ptr, s->d_prim_sil.ptr,
                                                        reinterpret_cast<LeafPrim<D> *>(s->d_leaf_prim.ptr), s->d_leaf_obj.ptr,
                                                        reinterpret_cast<LeafSil<D> *>(s->d_leaf_sil.ptr));
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_box, s->d_boxes.ptr, sizeof(float) * 2 * D, cudaMemcpyDeviceToHost, st));
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_cone, s->d_cones.ptr, sizeof(float) * (D + 2), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaMemcpyAsync(s->root_ext, ext.ptr, sizeof(float) * 2 * D, cudaMemcpyDeviceToHost, st));
         WOST_CUDA_TRY(s->d_overflow.alloc(1));
         WOST_CUDA_TRY(cudaMemsetAsync(s->d_overflow.ptr, 0, sizeof(int), st));
         WOST_CUDA_TRY(cudaStreamSynchronize(st));

@@ -1,5 +1,7 @@
 // Host-side scene object behind the opaque `wost_scene` handle.
 #pragma once
+#include <algorithm>
+#include <cmath>
 #include "common.cuh"
 #include "lbvh.cuh"
 
@@ -21,10 +23,11 @@ struct wost_scene
     wost::DevBuf<uint32_t> d_morton, d_order;
     // traversal layout
     wost::DevBuf<char> d_tnodes, d_cnodes, d_leaf_prim, d_leaf_sil;
-    wost::DevBuf<uint32_t> d_leaf_obj;
+    wost::DevBuf<uint32_t> d_leaf_obj, d_leaf_rank;
     wost::DevBuf<int> d_overflow;
     float root_box[6] = {0, 0, 0, 0, 0, 0};
     float root_cone[5] = {0, 0, 0, 0, 0};
+    float root_ext[6] = {0, 0, 0, 0, 0, 0}; // exact (unpadded) extents of the whole mesh
 
     template <int D>
     wost::DevBVH<D> view() const
@@ -35,11 +38,16 @@ struct wost_scene
         b.cnodes = reinterpret_cast<const wost::CNode<D> *>(d_cnodes.ptr);
         b.leaf_prim = reinterpret_cast<const wost::LeafPrim<D> *>(d_leaf_prim.ptr);
         b.leaf_obj = d_leaf_obj.ptr;
+        b.leaf_rank = d_leaf_rank.ptr;
         b.leaf_sil = reinterpret_cast<const wost::LeafSil<D> *>(d_leaf_sil.ptr);
         for (int k = 0; k < 2 * D; ++k)
             b.root_box[k] = root_box[k];
         for (int k = 0; k < D + 2; ++k)
             b.root_cone[k] = root_cone[k];
+        float m = 0.0f;
+        for (int k = 0; k < 2 * D; ++k)
+            m = std::max(m, std::fabs(root_ext[k]));
+        b.max_abs_coord = m;
         return b;
     }
 };
@@ -55,6 +63,8 @@ namespace wost
         b.cnodes = nullptr;
         b.leaf_prim = nullptr;
         b.leaf_obj = nullptr;
+        b.leaf_rank = nullptr;
+        b.max_abs_coord = 0.0f;
         b.leaf_sil = nullptr;
         for (int k = 0; k < 2 * D; ++k)
             b.root_box[k] = 0.0f;

@@ -293,7 +293,9 @@ namespace wost
 
     // ---------------------------------------------------------------------------------------------------------
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
-    template <int D>
+    // RefOrder: closest-point queries visit the tree in the reference's own order (query_nearest_ref) -- same results,
+    // kept as the on-device stand-in for the reference's traversal cost (bench.py --walk-mode reforder).
+    template <int D, bool RefOrder>
     WOST_DEV bool walk_step_uniform(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc)
     {
         const float eps = c.eps;
@@ -302,7 +304,10 @@ namespace wost
         if (c.dir.nprims > 0)
         {
             uint32_t pos;
-            query_nearest(c.dir, w.x, st, pos, R_D);
+            if (RefOrder)
+                query_nearest_ref(c.dir, w.x, st, pos, R_D);
+            else
+                query_nearest(c.dir, w.x, st, pos, R_D);
             if (R_D < eps)
             {
                 const Prim<D> pr = load_prim(c.dir.leaf_prim + pos);

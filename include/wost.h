@@ -115,8 +115,9 @@ extern "C"
     } wost_channel;
     typedef enum wost_walk_mode
     {
-        WOST_MODE_WAVEFRONT = 0, /* one fused kernel per bounce over compacted SoA queues */
-        WOST_MODE_PERSISTENT = 1 /* register-resident walks, persistent threads pulling (pixel, sample) jobs */
+        WOST_MODE_WAVEFRONT = 0,      /* one fused kernel per bounce over compacted SoA queues */
+        WOST_MODE_REFERENCE_ORDER = 2 /* same kernel, closest-point queries in the reference's visit order (core/query.cuh:238-318):
+                                         identical results; the on-device stand-in for the reference's traversal cost */
     } wost_walk_mode;
 
     typedef struct wost_settings /* IntegratorSettings: integrator/uniform/integrator.h:28-49, guided/integrator.h:56-90 */
@@ -154,6 +155,9 @@ extern "C"
     wost_status wost_film_device_ptr(wost_integrator *it, int channel, void **d_ptr);
     /* counters of the last solve */
     wost_status wost_last_launch_count(wost_integrator *it, uint64_t *kernel_launches);
+    /* launches of the fused walk-step kernel in the last solve and their summed device time (CUDA events on the
+     * integrator's stream around each spp batch's run of step launches) -- the roofline numerator of bench.py */
+    wost_status wost_last_step_kernel_time(wost_integrator *it, uint64_t *step_launches, float *step_kernel_ms);
 
 #ifdef __cplusplus
 }

@@ -122,3 +122,24 @@ def test_full_size_query_properties():
     np.testing.assert_allclose(dist, direct, rtol=1e-4, atol=1e-6)
     _, dv = s.nearest(v)
     assert np.all(dv <= 1e-6)
+
+
+@pytest.mark.parametrize("name", ["star10k", "ico5", "soup2d_random", "soup3d_random"])
+def test_nearest_tie_breaks_and_far_queries(oracle, name):
+    """The B200 traversal order must reproduce the reference's winner among EXACT ties (queries on vertices, on edge
+    midpoints, on the medial axis of a symmetric shape) and for far-away / huge-coordinate queries."""
+    api = _api()
+    dim, v, p = _scene_cases()[name]
+    so = oracle.scene(dim, v, p)
+    sg = api.Scene(dim, v, p)
+    rng = np.random.RandomState(5)
+    vq = v[rng.randint(0, len(v), 4000)]
+    mid = v[p[rng.randint(0, len(p), 4000)]].mean(1).astype(np.float32)
+    off = (vq + rng.randn(*vq.shape).astype(np.float32) * 1e-4).astype(np.float32)
+    far = (rng.randn(4000, dim) * np.array([10.0, 1e3, 1e5, 1e7])[rng.randint(0, 4, 4000)][:, None]).astype(np.float32)
+    centre = np.zeros((1, dim), np.float32) + v.mean(0).astype(np.float32)
+    for q in (vq, mid, off, far, centre):
+        io, do = so.nearest(q)
+        ig, dg = sg.nearest(q)
+        assert np.array_equal(io, ig)
+        assert np.array_equal(bits(do), bits(dg))

@@ -145,3 +145,17 @@ def test_sharding_is_invisible():
         parts.append(it.film()[..., :3])
     assert steps == full.last_walk_steps
     assert np.array_equal(bits(parts[0] + parts[1]), bits(full.film()[..., :3]))
+
+
+def test_reference_order_mode_is_identical(oracle):
+    """walk_mode=2 (closest-point queries in the reference's visit order) and the default B200 order give the same film."""
+    from elaina_b200 import api
+    spec = mixed_problem_2d(600)
+    _, gprob = build_both(oracle, spec)
+    films = []
+    for mode in (0, 2):
+        it = api.UniformIntegrator(gprob, api.make_settings((48, 48), 24, 4, 5e-3, seed=21, spp_batch=2, walk_mode=mode))
+        it.solve()
+        films.append((it.film()[..., :3].copy(), it.last_walk_steps))
+    assert films[0][1] == films[1][1]
+    assert np.array_equal(bits(films[0][0]), bits(films[1][0]))
