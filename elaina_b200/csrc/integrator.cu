@@ -92,9 +92,10 @@ namespace wost
             if (base >= n)
                 break;
             const long long i = base + lane;
+            const bool valid = i < n;
             bool alive = false;
             WalkState<D> w;
-            if (i < n)
+            if (valid)
             {
                 if (First)
                 {
@@ -110,9 +111,19 @@ namespace wost
                 }
                 else
                     load_item(a.in, (size_t)i, w);
+            }
+            else
+            {
+                w.pixel = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
+#pragma unroll
+                for (int k = 0; k < D; ++k)
+                    w.x[k] = w.nN[k] = 0.0f;
+            }
+            {
+                // every lane of the warp enters the step (the closest-point traversal is warp-synchronous)
                 PixelAcc acc;
                 acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
-                alive = walk_step_uniform<D, RefOrder>(c, w, a.depth, st, acc);
+                alive = walk_step_uniform<D, RefOrder>(c, w, a.depth, st, acc, valid);
                 acc.flush();
             }
             if (!a.last_depth)
@@ -161,21 +172,25 @@ namespace wost
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
         st.init(smem_stack, overflow);
-        for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x)
+        for (int base = blockIdx.x * blockDim.x; base < npix; base += gridDim.x * blockDim.x)
         {
-            const Vec<D> x = eval_point(c, (uint32_t)p);
+            const int p = base + threadIdx.x;
+            const bool valid = p < npix;
+            const Vec<D> x = eval_point(c, (uint32_t)(valid ? p : 0));
             float v[3] = {0.0f, 0.0f, 0.0f};
-            if (channel == WOST_CH_DIRICHLET_SDF)
+            if (channel == WOST_CH_DIRICHLET_SDF) // uniform branch: query_nearest is warp-synchronous
             {
                 float d = dm_inf();
                 if (c.dir.nprims > 0)
                 {
                     uint32_t pos;
-                    query_nearest(c.dir, x, st, pos, d);
+                    query_nearest(c.dir, x, st, pos, d, valid);
                 }
                 v[0] = v[1] = v[2] = d;
             }
-            else if (channel == WOST_CH_NEUMANN_SDF)
+            if (!valid)
+                continue;
+            if (channel == WOST_CH_NEUMANN_SDF)
             {
                 float d = dm_inf();
                 if (c.neu.nprims > 0)

@@ -230,13 +230,16 @@ namespace wost
     // Shared-memory stack, one column per thread: entry(level, tid) = base[level * blockDim + tid].
     // Consecutive lanes hit consecutive 8-byte slots -> conflict-free. The first kSmemLevels levels live in shared memory, deeper ones
     // (real scenes need <= 26 in total) spill to local memory; beyond 64 (the reference's limit) a flag is raised.
-    constexpr int kSmemLevels = 24; // short stack in shared memory
-    constexpr int kSpillLevels = 40; // deeper levels spill to local memory (reference limit: 64 in total)
+    constexpr int kSmemLevels = 32; // short stack in shared memory
+    constexpr int kSpillLevels = 32; // deeper levels spill to local memory (reference limit: 64 in total)
     struct StackEntry
     {
         uint32_t ref;
         float d;
     };
+    // cold path of the stack, kept out of line so that the hot loop carries no local-memory traffic
+    static __device__ __noinline__ void spill_store(uint2 *spill, int i, uint2 e) { spill[i] = e; }
+    static __device__ __noinline__ uint2 spill_load(const uint2 *spill, int i) { return spill[i]; }
     struct SmemStack
     {
         uint2 *base; // column of this thread (already offset by tid)
@@ -254,10 +257,10 @@ namespace wost
         WOST_DEV void push(uint32_t ref, float d)
         {
             const uint2 e = make_uint2(ref, __float_as_uint(d));
-            if (sp < kSmemLevels)
+            if (__builtin_expect(sp < kSmemLevels, 1))
                 base[sp * stride] = e;
             else if (sp < kSmemLevels + kSpillLevels)
-                spill[sp - kSmemLevels] = e;
+                spill_store(spill, sp - kSmemLevels, e);
             else
             {
                 if (overflow)
@@ -269,7 +272,11 @@ namespace wost
         WOST_DEV StackEntry pop()
         {
             --sp;
-            const uint2 e = (sp < kSmemLevels) ? base[sp * stride] : spill[sp - kSmemLevels];
+            uint2 e;
+            if (__builtin_expect(sp < kSmemLevels, 1))
+                e = base[sp * stride];
+            else
+                e = spill_load(spill, sp - kSmemLevels);
             StackEntry r;
             r.ref = e.x;
             r.d = __uint_as_float(e.y);
@@ -280,112 +287,120 @@ namespace wost
     inline size_t stack_smem_bytes(int block_threads) { return (size_t)block_threads * kSmemLevels * sizeof(uint2); }
 
     // ---------------------------------------------------------------- closest primitive (core/query.cuh:238-318)
-    // Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]) and the distance.
-    // Visit order mirrors the reference: L handled before R, leaves evaluated immediately, internal children
-    // pushed L then R (R popped first); "<=" keeps the last visited of exact ties.
+    // All closest-point traversals below are WARP-SYNCHRONOUS: the 32 lanes of a warp call them together (lanes without
+    // a query pass valid = false) and the traversal loop is `while (__any_sync(full, active))`, so the warp reconverges
+    // once per visited node instead of wherever the compiler places the loop's reconvergence point (a divergent
+    // `continue` in a per-thread loop left 4-8 of 32 lanes active in the first version, profiles/r1_notes.md).
+    constexpr uint32_t kFullMask = 0xffffffffu;
+
+    // Reference visit order: L handled before R, leaf children evaluated at once, internal children pushed L then R
+    // (R popped first); "<=" keeps the last visited of exact ties; a popped node is skipped when its padded mindist
+    // exceeds the running best. Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]).
     // Restricted = true: additionally skip every child whose EXACT-extent mindist exceeds thrW. Used as the second pass
     // of query_nearest: with thrW a little above the final minimum only the subtrees that can hold the (near-)tied
-    // minima are walked, in the reference's order and with the reference's own pop-time test on the padded mindist, so
-    // the winner among ties and near-ties is the reference's even where that depends on its visit order.
+    // minima are walked, in the reference's order and with the reference's own pop-time test, so the winner among
+    // ties and near-ties is the reference's even where that depends on its visit order.
     template <int D, bool Restricted>
-    WOST_DEV void query_nearest_ref_impl(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, float thrW, uint32_t &leaf_pos, float &dist)
+    WOST_DEV void query_nearest_ref_impl(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, float thrW, uint32_t &leaf_pos, float &dist, bool valid)
     {
-        leaf_pos = kInvalid;
-        float best = dm_inf();
         if (bvh.nprims <= 0)
         {
-            dist = best;
+            if (valid)
+            {
+                leaf_pos = kInvalid;
+                dist = dm_inf();
+            }
             return;
         }
         if (bvh.nprims == 1)
         {
-            const float d = prim_distance(load_prim(bvh.leaf_prim), q);
-            leaf_pos = 0;
-            dist = dm_sqrt(d * d);
+            if (valid)
+            {
+                const float d = prim_distance(load_prim(bvh.leaf_prim), q);
+                leaf_pos = 0;
+                dist = dm_sqrt(d * d);
+            }
             return;
         }
+        uint32_t win = kInvalid;
+        float best = dm_inf();
         st.sp = 0;
         uint32_t node = 0;
-        float node_d = box_mindist(root_box_of(bvh), q);
+        float node_d = valid ? box_mindist(root_box_of(bvh), q) : 0.0f;
         bool have = true;
-        while (true)
+        bool active = valid;
+        while (__any_sync(kFullMask, active))
         {
-            if (!have)
+            if (active)
             {
-                if (st.empty())
-                    break;
-                const StackEntry e = st.pop();
-                node = e.ref;
-                node_d = e.d;
-            }
-            have = false;
-            if (node_d > best)
-                continue;
-            const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
-            const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
-            const float Lmin = box_mindist(lp, q), Rmin = box_mindist(rp, q);
-            const float Lmm = box_minmaxdist(lp, q), Rmm = box_minmaxdist(rp, q);
-            bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
-            if (Restricted)
-            {
-                goL = goL && box_mindist(n.le, q) <= thrW;
-                goR = goR && box_mindist(n.re, q) <= thrW;
-            }
-            bool pushL = false;
-            if (goL)
-            {
-                if (n.lref & kLeafFlag)
+                if (!have)
                 {
-                    const uint32_t pos = n.lref & ~kLeafFlag;
-                    float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
-                    d *= d;
-                    if (d <= best)
+                    if (st.empty())
+                        active = false;
+                    else
                     {
-                        best = d;
-                        leaf_pos = pos;
+                        const StackEntry e = st.pop();
+                        node = e.ref;
+                        node_d = e.d;
                     }
                 }
-                else
-                    pushL = true;
-            }
-            if (goR)
-            {
-                if (n.rref & kLeafFlag)
+                have = false;
+                if (active && !(node_d > best))
                 {
-                    const uint32_t pos = n.rref & ~kLeafFlag;
-                    float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
-                    d *= d;
-                    if (d <= best)
+                    const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
+                    const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
+                    const float Lmin = box_mindist(lp, q), Rmin = box_mindist(rp, q);
+                    const float Lmm = box_minmaxdist(lp, q), Rmm = box_minmaxdist(rp, q);
+                    bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
+                    if (Restricted)
                     {
-                        best = d;
-                        leaf_pos = pos;
+                        goL = goL && box_mindist(n.le, q) <= thrW;
+                        goR = goR && box_mindist(n.re, q) <= thrW;
+                    }
+#pragma unroll
+                    for (int side = 0; side < 2; ++side)
+                    {
+                        const uint32_t ref = side == 0 ? n.lref : n.rref;
+                        if ((side == 0 ? goL : goR) && (ref & kLeafFlag))
+                        {
+                            const uint32_t pos = ref & ~kLeafFlag;
+                            float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
+                            d *= d;
+                            if (d <= best)
+                            {
+                                best = d;
+                                win = pos;
+                            }
+                        }
+                    }
+                    const bool inL = goL && !(n.lref & kLeafFlag), inR = goR && !(n.rref & kLeafFlag);
+                    if (inL && inR)
+                        st.push(n.lref, Lmin); // R would be pushed last and popped next: keep it in registers
+                    if (inR)
+                    {
+                        node = n.rref;
+                        node_d = Rmin;
+                        have = true;
+                    }
+                    else if (inL)
+                    {
+                        node = n.lref;
+                        node_d = Lmin;
+                        have = true;
                     }
                 }
-                else
-                {
-                    // R would be pushed last and popped next: keep it in registers
-                    if (pushL)
-                        st.push(n.lref, Lmin);
-                    pushL = false;
-                    node = n.rref;
-                    node_d = Rmin;
-                    have = true;
-                }
-            }
-            if (pushL)
-            {
-                // only L is internal: it is the next pop
-                node = n.lref;
-                node_d = Lmin;
-                have = true;
             }
         }
-        dist = dm_sqrt(best);
+        if (valid)
+        {
+            leaf_pos = win;
+            dist = dm_sqrt(best);
+        }
     }
     template <int D>
-    WOST_DEV void query_nearest_ref(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist)
+    WOST_DEV void query_nearest_ref(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid = true)
     {
-        query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist);
+        query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist, valid);
     }
 
     // ---------------------------------------------------------------- closest primitive, B200 traversal order
@@ -394,12 +409,13 @@ namespace wost
     //   * the reference's sibling rule "mindist(child) <= minmaxdist(sibling)" (query.cuh:279,299) is evaluated on the
     //     rebuilt padded boxes exactly as the reference does -- it is local to a node, hence independent of visit order,
     //     and it defines the candidate set S of leaves the reference can ever reach;
-    //   * pruning by the running best is free to be aggressive: children are visited nearest first and a child is
-    //     dropped as soon as the mindist of its EXACT extent exceeds (sqrt(best) + slack)^2, also at leaf level (the
-    //     reference only tests at pop time, on padded boxes, in fixed L/R order). slack = 2^-19 * max |coordinate|
-    //     (>= 16 ulp) covers the rounding of the leaf distance itself, so no (near-)minimal leaf is dropped;
+    //   * pruning by the running best is free to be aggressive: children (internal nodes and leaves alike) are visited
+    //     nearest first and dropped as soon as the mindist of their EXACT extent exceeds (sqrt(best) + slack)^2 (the
+    //     reference only tests internal nodes, at pop time, on padded boxes, in fixed L/R order). slack = 2^-19 * max
+    //     |coordinate| (>= 16 ulp) covers the rounding of the leaf distance itself, so no (near-)minimal leaf is dropped;
     //   * the sqrt + re-square of the reference (dist = length(..); dist *= dist) is only done for leaves whose squared
-    //     length can still win (x -> fl(fl(sqrt x)^2) is monotone and within 3 ulp of x).
+    //     length can still win (x -> fl(fl(sqrt x)^2) is monotone and within 3 ulp of x);
+    //   * one stack entry type for nodes and leaves: per loop trip a lane either opens a node or evaluates a leaf.
     // Which leaf the reference returns among EXACT ties (shared vertices / edges):
     //   * 2D (boxes padded by 1e-3, scene.cuh:12): the reference's pop-time test can never drop a tied minimum, so it
     //     returns the last visited one of its static order == the highest leaf_rank. No second pass.
@@ -409,13 +425,11 @@ namespace wost
     //     (query_nearest_ref_impl<Restricted>) and takes its answer.
     //   * far field (|q| beyond ~1000x the mesh, where fp32 collapses all distances): the reference order itself.
     template <int D>
-    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist)
+    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid = true)
     {
-        leaf_pos = kInvalid;
-        float best = dm_inf(); // re-squared distance of the winner, as the reference keeps it
-        if (bvh.nprims <= 0)
+        if (bvh.nprims <= 1)
         {
-            dist = best;
+            query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist, valid);
             return;
         }
         float qmax = 0.0f;
@@ -423,111 +437,128 @@ namespace wost
         for (int k = 0; k < D; ++k)
             qmax = fmax_nn(qmax, dm_abs(q[k]));
         const bool far = qmax > 1024.0f * bvh.max_abs_coord || (D == 2 && qmax > 2000.0f);
-        if (bvh.nprims == 1 || far)
-        {
-            query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist);
-            return;
-        }
         const float slack = fmax_nn(qmax, bvh.max_abs_coord) * 1.9073486328125e-06f; // 2^-19
-        float thr = dm_inf();                                                          // (sqrt(best) + slack)^2
+        uint32_t win = kInvalid;
+        float best = dm_inf(); // re-squared distance of the winner, as the reference keeps it
+        float thr = dm_inf();  // (sqrt(best) + slack)^2
         uint32_t best_rank = 0;
         bool have_rank = false;
         int n_near = 0; // leaves seen within 8 ulp of the running minimum (3D tie detection)
         st.sp = 0;
-        uint32_t node = 0;
-        for (;;)
+        uint32_t cur = 0;
+        float cur_d = 0.0f;
+        bool active = valid && !far;
+        while (__any_sync(kFullMask, active))
         {
-            const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
-            const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
-            const float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
-            bool goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
-            bool goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
-#pragma unroll
-            for (int side = 0; side < 2; ++side)
+            if (active)
             {
-                const uint32_t ref = side == 0 ? n.lref : n.rref;
-                const bool go = side == 0 ? goL : goR;
-                const float e = side == 0 ? Le : Re;
-                if (go && (ref & kLeafFlag) && e <= thr)
+                bool have = false;
+                if (cur & kLeafFlag)
                 {
-                    const uint32_t pos = ref & ~kLeafFlag;
-                    const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
-                    if (d2 <= best * 1.000002f)
+                    if (cur_d <= thr)
                     {
-                        const float d = dm_sqrt(d2);
-                        const float g = d * d;
-                        bool take = g < best;
-                        if (D == 3)
+                        const uint32_t pos = cur & ~kLeafFlag;
+                        const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
+                        if (d2 <= best * 1.000002f)
                         {
-                            if (take)
-                                n_near = (best <= g * 1.000001f) ? n_near + 1 : 1;
-                            else if (g <= best * 1.000001f)
-                                ++n_near;
-                        }
-                        if (take)
-                            have_rank = false;
-                        else if (D == 2 && g == best && leaf_pos != kInvalid)
-                        {
-                            // exact tie: the reference keeps the last visited leaf of its own (static) order
-                            const uint32_t rk = __ldg(bvh.leaf_rank + pos);
-                            if (!have_rank)
+                            const float d = dm_sqrt(d2);
+                            const float g = d * d;
+                            bool take = g < best;
+                            if (D == 3)
                             {
-                                best_rank = __ldg(bvh.leaf_rank + leaf_pos);
-                                have_rank = true;
+                                if (take)
+                                    n_near = (best <= g * 1.000001f) ? n_near + 1 : 1;
+                                else if (g <= best * 1.000001f)
+                                    ++n_near;
                             }
-                            take = rk > best_rank;
                             if (take)
-                                best_rank = rk;
+                                have_rank = false;
+                            else if (D == 2 && g == best && win != kInvalid)
+                            {
+                                // exact tie: the reference keeps the last visited leaf of its own (static) order
+                                const uint32_t rk = __ldg(bvh.leaf_rank + pos);
+                                if (!have_rank)
+                                {
+                                    best_rank = __ldg(bvh.leaf_rank + win);
+                                    have_rank = true;
+                                }
+                                take = rk > best_rank;
+                                if (take)
+                                    best_rank = rk;
+                            }
+                            if (take)
+                            {
+                                best = g;
+                                win = pos;
+                                const float t = d + slack;
+                                thr = t * t;
+                            }
                         }
-                        if (take)
+                    }
+                }
+                else
+                {
+                    const NodeViewE<D> n = load_tnode_e(bvh.tnodes + cur);
+                    const float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
+                    bool goL = Le <= thr, goR = Re <= thr;
+                    if (goL || goR)
+                    {
+                        const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
+                        if (goL)
+                            goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
+                        if (goR)
+                            goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
+                        if (goL && goR)
                         {
-                            best = g;
-                            leaf_pos = pos;
-                            const float t = d + slack;
-                            thr = t * t;
+                            const bool lnear = Le <= Re;
+                            st.push(lnear ? n.rref : n.lref, lnear ? Re : Le);
+                            cur = lnear ? n.lref : n.rref;
+                            cur_d = lnear ? Le : Re;
+                            have = true;
+                        }
+                        else if (goL || goR)
+                        {
+                            cur = goL ? n.lref : n.rref;
+                            cur_d = goL ? Le : Re;
+                            have = true;
+                        }
+                    }
+                }
+                if (!have)
+                {
+                    active = false;
+                    while (!st.empty())
+                    {
+                        const StackEntry e = st.pop();
+                        if (e.d <= thr)
+                        {
+                            cur = e.ref;
+                            cur_d = e.d;
+                            active = true;
+                            break;
                         }
                     }
                 }
             }
-            goL = goL && !(n.lref & kLeafFlag) && Le <= thr;
-            goR = goR && !(n.rref & kLeafFlag) && Re <= thr;
-            if (goL && goR)
-            {
-                const bool lnear = Le <= Re;
-                st.push(lnear ? n.rref : n.lref, lnear ? Re : Le);
-                node = lnear ? n.lref : n.rref;
-                continue;
-            }
-            if (goL)
-            {
-                node = n.lref;
-                continue;
-            }
-            if (goR)
-            {
-                node = n.rref;
-                continue;
-            }
-            bool found = false;
-            while (!st.empty())
-            {
-                const StackEntry e = st.pop();
-                if (e.d <= thr)
-                {
-                    node = e.ref;
-                    found = true;
-                    break;
-                }
-            }
-            if (!found)
-                break;
         }
-        if (D == 3 && n_near > 1)
+        const bool pass2 = valid && (far || (D == 3 && n_near > 1));
+        if (__any_sync(kFullMask, pass2))
         {
-            query_nearest_ref_impl<D, true>(bvh, q, st, thr, leaf_pos, dist);
-            return;
+            uint32_t win2 = kInvalid;
+            float dist2 = 0.0f;
+            query_nearest_ref_impl<D, true>(bvh, q, st, far ? dm_inf() : thr, win2, dist2, pass2);
+            if (pass2)
+            {
+                leaf_pos = win2;
+                dist = dist2;
+                return;
+            }
         }
-        dist = dm_sqrt(best);
+        if (valid)
+        {
+            leaf_pos = win;
+            dist = dm_sqrt(best);
+        }
     }
 
     // ---------------------------------------------------------------- closest silhouette (core/query.cuh:325-423)

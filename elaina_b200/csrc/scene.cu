@@ -873,18 +873,24 @@ namespace wost
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
         st.init(smem_stack, overflow);
-        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        // warp-uniform trip count: query_nearest is warp-synchronous (lanes past the end pass valid = false)
+        for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x)
         {
+            const int i = base + threadIdx.x;
+            const bool valid = i < n;
             Vec<D> q;
 #pragma unroll
             for (int k = 0; k < D; ++k)
-                q[k] = pts[(size_t)i * D + k];
-            uint32_t pos;
-            float d;
-            query_nearest(bvh, q, st, pos, d);
-            if (idx)
-                idx[i] = (pos == kInvalid) ? kInvalid : __ldg(bvh.leaf_obj + pos);
-            dist[i] = d;
+                q[k] = valid ? pts[(size_t)i * D + k] : 0.0f;
+            uint32_t pos = kInvalid;
+            float d = 0.0f;
+            query_nearest(bvh, q, st, pos, d, valid);
+            if (valid)
+            {
+                if (idx)
+                    idx[i] = (pos == kInvalid) ? kInvalid : __ldg(bvh.leaf_obj + pos);
+                dist[i] = d;
+            }
         }
     }
     template <int D>

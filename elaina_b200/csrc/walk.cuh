@@ -296,18 +296,20 @@ namespace wost
     // RefOrder: closest-point queries visit the tree in the reference's own order (query_nearest_ref) -- same results,
     // kept as the on-device stand-in for the reference's traversal cost (bench.py --walk-mode reforder).
     template <int D, bool RefOrder>
-    WOST_DEV bool walk_step_uniform(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc)
+    WOST_DEV bool walk_step_uniform(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc, bool valid)
     {
         const float eps = c.eps;
         // ---- separate (integrator/uniform/integrator.cu:102-212)
         float R_D = dm_inf();
         if (c.dir.nprims > 0)
         {
-            uint32_t pos;
+            uint32_t pos = kInvalid;
             if (RefOrder)
-                query_nearest_ref(c.dir, w.x, st, pos, R_D);
+                query_nearest_ref(c.dir, w.x, st, pos, R_D, valid);
             else
-                query_nearest(c.dir, w.x, st, pos, R_D);
+                query_nearest(c.dir, w.x, st, pos, R_D, valid);
+            if (!valid)
+                return false;
             if (R_D < eps)
             {
                 const Prim<D> pr = load_prim(c.dir.leaf_prim + pos);
@@ -329,6 +331,8 @@ namespace wost
                 }
             }
         }
+        if (!valid)
+            return false;
         float R_N = dm_inf();
         if (c.neu.nprims > 0)
             R_N = query_silhouette(c.neu, w.x, false, st);
