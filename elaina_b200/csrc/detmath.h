@@ -63,8 +63,9 @@ DM_HD float dm_div(float a, float b) { return a / b; }
 // std::min / std::max semantics of the reference call sites (not NaN-suppressing): (b < a) ? b : a
 DM_HD float dm_min(float a, float b) { return (b < a) ? b : a; }
 DM_HD float dm_max(float a, float b) { return (a < b) ? b : a; }
-// ::fmin / ::fmax semantics (NaN-suppressing, IEEE minNum/maxNum)
-DM_HD float dm_fmin(float a, float b)
+// ::fmin / ::fmax semantics (NaN-suppressing, IEEE minNum/maxNum), written out so that host and device agree on
+// the sign of zero as well (used where the result is stored and compared bit for bit: box merges of the build)
+DM_HD float dm_fmin_strict(float a, float b)
 {
     if (dm_isnan(a))
         return b;
@@ -72,7 +73,7 @@ DM_HD float dm_fmin(float a, float b)
         return a;
     return (b < a) ? b : a;
 }
-DM_HD float dm_fmax(float a, float b)
+DM_HD float dm_fmax_strict(float a, float b)
 {
     if (dm_isnan(a))
         return b;
@@ -80,6 +81,15 @@ DM_HD float dm_fmax(float a, float b)
         return a;
     return (a < b) ? b : a;
 }
+// Hot-path flavour: one FMNMX on the device (same NaN suppression; may differ from the host only in the sign of a
+// zero result, which no caller can observe: the values are squared, compared or clamped to positive numbers).
+#if defined(__CUDA_ARCH__)
+DM_HD float dm_fmin(float a, float b) { return fminf(a, b); }
+DM_HD float dm_fmax(float a, float b) { return fmaxf(a, b); }
+#else
+DM_HD float dm_fmin(float a, float b) { return dm_fmin_strict(a, b); }
+DM_HD float dm_fmax(float a, float b) { return dm_fmax_strict(a, b); }
+#endif
 
 // ---------------------------------------------------------------- sin / cos
 // kernel on |r| <= pi/4

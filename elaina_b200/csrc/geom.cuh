@@ -101,8 +101,8 @@ namespace wost
 #pragma unroll
         for (int i = 0; i < D; ++i)
         {
-            m.up[i] = dm_fmax(a.up[i], b.up[i]);
-            m.lo[i] = dm_fmin(a.lo[i], b.lo[i]);
+            m.up[i] = dm_fmax_strict(a.up[i], b.up[i]);
+            m.lo[i] = dm_fmin_strict(a.lo[i], b.lo[i]);
         }
         return m;
     }

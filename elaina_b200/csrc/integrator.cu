@@ -78,7 +78,8 @@ namespace wost
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
-        st.init(smem_stack, a.overflow);
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, a.overflow, spill_mem);
         const int lane = threadIdx.x & 31;
         const long long n = First ? (long long)a.n_active * a.batch_samples : (long long)*a.in_count;
         if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0)
@@ -171,7 +172,8 @@ namespace wost
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
-        st.init(smem_stack, overflow);
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, overflow, spill_mem);
         for (int base = blockIdx.x * blockDim.x; base < npix; base += gridDim.x * blockDim.x)
         {
             const int p = base + threadIdx.x;

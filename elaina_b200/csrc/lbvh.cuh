@@ -246,9 +246,11 @@ namespace wost
         int stride;  // blockDim.x
         int sp;
         int *overflow;
-        uint2 spill[kSpillLevels];
-        WOST_DEV void init(uint2 *smem, int *overflow_flag)
+        uint2 *spill; // kSpillLevels entries of thread-local memory owned by the kernel (kept outside this struct so that the
+                      // struct itself -- sp, base -- stays in registers)
+        WOST_DEV void init(uint2 *smem, int *overflow_flag, uint2 *spill_mem)
         {
+            spill = spill_mem;
             base = smem + threadIdx.x;
             stride = blockDim.x;
             sp = 0;

@@ -178,8 +178,8 @@ namespace wost
 #pragma unroll
             for (int k = 0; k < 3; ++k)
             {
-                b.lo[k] = dm_fmin(b.lo[k], p[k] - kEps);
-                b.up[k] = dm_fmax(b.up[k], p[k] + kEps);
+                b.lo[k] = dm_fmin_strict(b.lo[k], p[k] - kEps);
+                b.up[k] = dm_fmax_strict(b.up[k], p[k] + kEps);
             }
         }
         return b;
@@ -202,8 +202,8 @@ namespace wost
 #pragma unroll
             for (int k = 0; k < D; ++k)
             {
-                b.lo[k] = dm_fmin(b.lo[k], p[k]);
-                b.up[k] = dm_fmax(b.up[k], p[k]);
+                b.lo[k] = dm_fmin_strict(b.lo[k], p[k]);
+                b.up[k] = dm_fmax_strict(b.up[k], p[k]);
             }
         }
         return b;
@@ -299,8 +299,8 @@ namespace wost
 #pragma unroll
             for (int k = 0; k < D; ++k)
             {
-                up[k] = dm_fmax(up[k], b.up[k]);
-                lo[k] = dm_fmin(lo[k], b.lo[k]);
+                up[k] = dm_fmax_strict(up[k], b.up[k]);
+                lo[k] = dm_fmin_strict(lo[k], b.lo[k]);
             }
         }
 #pragma unroll
@@ -317,8 +317,8 @@ namespace wost
 #pragma unroll
                 for (int k = 0; k < D; ++k)
                 {
-                    sh[k][threadIdx.x] = dm_fmax(sh[k][threadIdx.x], sh[k][threadIdx.x + s]);
-                    sh[D + k][threadIdx.x] = dm_fmin(sh[D + k][threadIdx.x], sh[D + k][threadIdx.x + s]);
+                    sh[k][threadIdx.x] = dm_fmax_strict(sh[k][threadIdx.x], sh[k][threadIdx.x + s]);
+                    sh[D + k][threadIdx.x] = dm_fmin_strict(sh[D + k][threadIdx.x], sh[D + k][threadIdx.x + s]);
                 }
             }
             __syncthreads();
@@ -355,7 +355,7 @@ namespace wost
             const float wl = whole[D + k], wu = whole[k];
             float x = p[k] - wl;
             x = dm_div(x, wu - wl);
-            x = dm_fmin(dm_fmax(x * 1024.0f, 0.0f), 1024.0f - 1.0f);
+            x = dm_fmin_strict(dm_fmax_strict(x * 1024.0f, 0.0f), 1024.0f - 1.0f);
             const uint32_t e = expand_bits((uint32_t)x);
             if (D == 2)
                 c = (k == 0) ? e * 2 : c + e;
@@ -872,7 +872,8 @@ namespace wost
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
-        st.init(smem_stack, overflow);
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, overflow, spill_mem);
         // warp-uniform trip count: query_nearest is warp-synchronous (lanes past the end pass valid = false)
         for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x)
         {
@@ -898,7 +899,8 @@ namespace wost
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
-        st.init(smem_stack, overflow);
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, overflow, spill_mem);
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         {
             Vec<D> q;
@@ -914,7 +916,8 @@ namespace wost
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
-        st.init(smem_stack, overflow);
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, overflow, spill_mem);
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         {
             Vec<D> o, d;
