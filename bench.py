@@ -191,7 +191,7 @@ def main():
     ap.add_argument("--workload", default="c3")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (reported in config)")
     ap.add_argument("--spp-batch", type=int, default=0)
-    ap.add_argument("--walk-mode", default="wavefront", choices=["wavefront", "reforder"],
+    ap.add_argument("--walk-mode", default="persistent", choices=["persistent", "wavefront", "reforder", "persistent-reforder"],
                     help="reforder: closest-point queries in the reference's visit order (stand-in for the reference's traversal cost)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg (line carries e2e: null)")
@@ -242,7 +242,7 @@ def main():
     # strong scaling: the frame is fixed, rows are dealt to ranks in interleaved tiles of 4 rows (pixel-keyed RNG ->
     # the summed film does not depend on N)
     shard = dict(pixel_stride_rows=4, num_shards=world, shard=rank) if world > 1 else {}
-    settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=args.spp_batch, walk_mode=2 if args.walk_mode == "reforder" else 0, **shard)
+    settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=args.spp_batch, walk_mode={"persistent": 1, "reforder": 2, "wavefront": 3, "persistent-reforder": 4}[args.walk_mode], **shard)
 
     def make_problem():
         g_d = api.Scene(dim, wl["dverts"], wl["dprims"])
@@ -344,7 +344,7 @@ def main():
                     "path": "wost_scene_create+LBVH build -> wost_problem_create -> wost_integrator_create -> wost_solve -> wost_film_download"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "kernel": "k_step_uniform<%d>" % dim, "bytes_per_walk_step": bps, "launches": int(kern_launches),
+                         "kernel": ("k_walk_persistent<%d>" if args.walk_mode.startswith("persistent") else "k_step_uniform<%d>") % dim, "bytes_per_walk_step": bps, "launches": int(kern_launches),
                          "avg_launch_ms": kern_ms / max(1, kern_launches), "kernel_share_of_step": kern_ms_max / dev_ms if dev_ms > 0 else None,
                          "peak_source": peak_src},
             "clocks": clocks,

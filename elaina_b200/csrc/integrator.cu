@@ -144,6 +144,119 @@ namespace wost
         }
     }
 
+    // ---------------------------------------------------------------------------------------------------------
+    // Persistent walk kernel (default mode): ONE launch per batch of S samples-per-pixel. Each lane owns a whole walk
+    // -- state in registers from the evaluation point to the epsilon-shell -- and the warp runs a two-phase loop:
+    //   traversal trips   every lane with a closest-point query in flight opens one node / evaluates one leaf;
+    //   tail + refill     as soon as kRefillThreshold lanes have finished their query (or nobody is traversing any
+    //                     more) those lanes run the rest of their walk step (walk_step_tail: epsilon-shell test,
+    //                     Dirichlet read-out, silhouette query, source / Neumann samples, direction sample + ray),
+    //                     lanes whose walk ended claim new (pixel, sample) jobs with one atomic per warp, and all of
+    //                     them start their next query.
+    // So the closest-point traversal -- >90% of the instructions -- runs with nearly all lanes busy although the
+    // number of visits per query varies 10x between neighbouring lanes, and a bounce costs neither a kernel launch nor a
+    // queue round trip through HBM. Same Philox stream (pixel, sample, depth) and same per-(slot, pixel) accumulators
+    // as the wavefront kernel, hence the same film bit for bit.
+    constexpr int kRefillThreshold = 8;
+
+    struct PersistArgs
+    {
+        const uint32_t *active;
+        int n_active;
+        uint32_t sample0;
+        int batch_samples;
+        float4 *acc; // [slot][pixel]
+        int npix;
+        int max_depth;
+        int *cursor;
+        unsigned long long *steps;
+        int *overflow;
+    };
+
+    template <int D, bool RefOrder>
+    __global__ void __launch_bounds__(kWalkBlock) k_walk_persistent(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ PersistArgs a)
+    {
+        extern __shared__ uint2 smem_stack[];
+        SmemStack st;
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, a.overflow, spill_mem);
+        const int lane = threadIdx.x & 31;
+        const long long njobs = (long long)a.n_active * a.batch_samples;
+        WalkState<D> w;
+        NearestTrav<D> t;
+        uint32_t depth = 0;
+        bool has_walk = false, exhausted = false, trav = false;
+        unsigned int my_steps = 0;
+        w.pixel = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            w.x[k] = w.nN[k] = 0.0f;
+        t.win = kInvalid, t.best = 0.0f;
+        for (;;)
+        {
+            const unsigned trav_mask = __ballot_sync(kFullMask, trav);
+            const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has_walk || !exhausted));
+            if (pend_mask != 0u && (__popc(pend_mask) >= kRefillThreshold || trav_mask == 0u))
+            {
+                if (!trav && has_walk)
+                {
+                    PixelAcc acc;
+                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
+                    const bool alive = walk_step_tail<D>(c, w, depth, st, acc, nearest_distance(t), t.win);
+                    acc.flush();
+                    ++depth;
+                    if (!alive || depth >= (uint32_t)a.max_depth)
+                        has_walk = false;
+                }
+                const bool want = !has_walk && !exhausted;
+                const unsigned want_mask = __ballot_sync(kFullMask, want);
+                if (want_mask != 0u)
+                {
+                    const int leader = __ffs(want_mask) - 1;
+                    int base = 0;
+                    if (lane == leader)
+                        base = atomicAdd(a.cursor, __popc(want_mask));
+                    base = __shfl_sync(kFullMask, base, leader);
+                    if (want)
+                    {
+                        const long long i = (long long)base + __popc(want_mask & ((1u << lane) - 1u));
+                        if (i < njobs)
+                        {
+                            const uint32_t sj = (uint32_t)(i / a.n_active);
+                            w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
+                            w.sample = a.sample0 + sj;
+                            w.x = eval_point(c, w.pixel);
+                            w.thp = 1.0f;
+                            w.onN = false;
+#pragma unroll
+                            for (int k = 0; k < D; ++k)
+                                w.nN[k] = 0.0f;
+                            depth = 0;
+                            has_walk = true;
+                        }
+                        else
+                            exhausted = true;
+                    }
+                }
+                if (!trav && has_walk)
+                {
+                    ++my_steps;
+                    trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t);
+                }
+            }
+            else if (trav_mask == 0u)
+                break;
+            if (trav)
+                trav = nearest_trip<D, RefOrder>(c.dir, w.x, st, t);
+        }
+        unsigned int ws = my_steps;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+            ws += __shfl_xor_sync(kFullMask, ws, o);
+        if (lane == 0 && ws)
+            atomicAdd(a.steps, (unsigned long long)ws);
+    }
+
     // solution/spp -> Film (integrator.cu:614-620): {r,g,b,1, weight 1}; slots are summed in slot order
     __global__ void k_resolve(int npix, int nslots, const float4 *acc, float inv_spp, const uint32_t *owned_begin_end, float *film)
     {
@@ -283,6 +396,83 @@ namespace wost
                 }
                 WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));
             }
+        }
+        k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
+        ++it->launches;
+        WOST_CUDA_TRY(cudaGetLastError());
+        unsigned long long h_steps = 0;
+        int h_over = 0;
+        WOST_CUDA_TRY(cudaMemcpyAsync(&h_steps, it->d_steps.ptr, sizeof(h_steps), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaMemcpyAsync(&h_over, it->d_overflow.ptr, sizeof(int), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaEventRecord(it->ev1, st));
+        WOST_CUDA_TRY(cudaStreamSynchronize(st));
+        if (walk_steps)
+            *walk_steps = h_steps;
+        for (int bi = 0; bi < nbatches; ++bi)
+        {
+            float f = 0.0f;
+            WOST_CUDA_TRY(cudaEventElapsedTime(&f, it->batch_ev[2 * bi], it->batch_ev[2 * bi + 1]));
+            it->step_kernel_ms += f;
+        }
+        if (h_over)
+        {
+            cudaMemsetAsync(it->d_overflow.ptr, 0, sizeof(int), st);
+            set_last_error("LBVH traversal stack overflow during solve");
+            return WOST_ERR_OVERFLOW;
+        }
+        return WOST_OK;
+    }
+    template <int D, bool RefOrder>
+    static wost_status solve_persistent(wost_integrator *it, uint64_t *walk_steps)
+    {
+        WalkCtx<D> ctx;
+        it->problem->fill_ctx(ctx);
+        ctx.frame_w = it->s.frame_w;
+        ctx.frame_h = it->s.frame_h;
+        ctx.max_depth = it->s.max_walking_depth;
+        ctx.eps = it->s.epsilon_shell;
+        ctx.seed = it->s.seed;
+        const int S = it->spp_batch;
+        const int spp = it->s.samples_per_pixel;
+        cudaStream_t st = it->stream;
+        const size_t smem = stack_smem_bytes(kWalkBlock);
+        int occ = 1;
+        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_walk_persistent<D, RefOrder>, kWalkBlock, smem));
+        const int grid_full = sm_count() * std::max(1, occ);
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
+        it->launches = 0;
+        it->step_launches = 0;
+        it->step_kernel_ms = 0.0f;
+        const int nbatches = it->n_active > 0 ? (spp + S - 1) / S : 0;
+        while ((int)it->batch_ev.size() < 2 * nbatches)
+        {
+            cudaEvent_t e;
+            WOST_CUDA_TRY(cudaEventCreate(&e));
+            it->batch_ev.push_back(e);
+        }
+        for (int s0 = 0, bi = 0; bi < nbatches; s0 += S, ++bi)
+        {
+            const int Sb = std::min(S, spp - s0);
+            WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int), st));
+            WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi], st));
+            PersistArgs a;
+            a.active = it->d_active.ptr;
+            a.n_active = it->n_active;
+            a.sample0 = (uint32_t)s0;
+            a.batch_samples = Sb;
+            a.acc = it->d_acc.ptr;
+            a.npix = it->npix;
+            a.max_depth = it->s.max_walking_depth;
+            a.cursor = it->d_counts.ptr;
+            a.steps = it->d_steps.ptr;
+            a.overflow = it->d_overflow.ptr;
+            const long long n0 = (long long)it->n_active * Sb;
+            const int grid = (int)std::min<long long>(grid_full, (n0 + kWalkBlock - 1) / kWalkBlock);
+            k_walk_persistent<D, RefOrder><<<std::max(1, grid), kWalkBlock, smem, st>>>(ctx, a);
+            ++it->launches;
+            ++it->step_launches;
+            WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));
         }
         k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
         ++it->launches;
@@ -502,10 +692,21 @@ extern "C"
         const auto t0 = std::chrono::high_resolution_clock::now();
         WOST_CUDA_TRY(cudaEventRecord(it->ev0, it->stream));
         wost_status rc;
-        if (it->s.walk_mode == WOST_MODE_REFERENCE_ORDER)
+        switch (it->s.walk_mode)
+        {
+        case WOST_MODE_REFERENCE_ORDER:
             rc = (it->dim == 2) ? solve_uniform<2, true>(it, walk_steps) : solve_uniform<3, true>(it, walk_steps);
-        else
+            break;
+        case WOST_MODE_WAVEFRONT:
             rc = (it->dim == 2) ? solve_uniform<2, false>(it, walk_steps) : solve_uniform<3, false>(it, walk_steps);
+            break;
+        case WOST_MODE_PERSISTENT_REFERENCE_ORDER:
+            rc = (it->dim == 2) ? solve_persistent<2, true>(it, walk_steps) : solve_persistent<3, true>(it, walk_steps);
+            break;
+        default:
+            rc = (it->dim == 2) ? solve_persistent<2, false>(it, walk_steps) : solve_persistent<3, false>(it, walk_steps);
+            break;
+        }
         if (rc != WOST_OK)
             return rc;
         const auto t1 = std::chrono::high_resolution_clock::now();

@@ -289,125 +289,21 @@ namespace wost
     inline size_t stack_smem_bytes(int block_threads) { return (size_t)block_threads * kSmemLevels * sizeof(uint2); }
 
     // ---------------------------------------------------------------- closest primitive (core/query.cuh:238-318)
-    // All closest-point traversals below are WARP-SYNCHRONOUS: the 32 lanes of a warp call them together (lanes without
-    // a query pass valid = false) and the traversal loop is `while (__any_sync(full, active))`, so the warp reconverges
-    // once per visited node instead of wherever the compiler places the loop's reconvergence point (a divergent
-    // `continue` in a per-thread loop left 4-8 of 32 lanes active in the first version, profiles/r1_notes.md).
-    constexpr uint32_t kFullMask = 0xffffffffu;
-
-    // Reference visit order: L handled before R, leaf children evaluated at once, internal children pushed L then R
-    // (R popped first); "<=" keeps the last visited of exact ties; a popped node is skipped when its padded mindist
-    // exceeds the running best. Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]).
-    // Restricted = true: additionally skip every child whose EXACT-extent mindist exceeds thrW. Used as the second pass
-    // of query_nearest: with thrW a little above the final minimum only the subtrees that can hold the (near-)tied
-    // minima are walked, in the reference's order and with the reference's own pop-time test, so the winner among
-    // ties and near-ties is the reference's even where that depends on its visit order.
-    template <int D, bool Restricted>
-    WOST_DEV void query_nearest_ref_impl(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, float thrW, uint32_t &leaf_pos, float &dist, bool valid)
-    {
-        if (bvh.nprims <= 0)
-        {
-            if (valid)
-            {
-                leaf_pos = kInvalid;
-                dist = dm_inf();
-            }
-            return;
-        }
-        if (bvh.nprims == 1)
-        {
-            if (valid)
-            {
-                const float d = prim_distance(load_prim(bvh.leaf_prim), q);
-                leaf_pos = 0;
-                dist = dm_sqrt(d * d);
-            }
-            return;
-        }
-        uint32_t win = kInvalid;
-        float best = dm_inf();
-        st.sp = 0;
-        uint32_t node = 0;
-        float node_d = valid ? box_mindist(root_box_of(bvh), q) : 0.0f;
-        bool have = true;
-        bool active = valid;
-        while (__any_sync(kFullMask, active))
-        {
-            if (active)
-            {
-                if (!have)
-                {
-                    if (st.empty())
-                        active = false;
-                    else
-                    {
-                        const StackEntry e = st.pop();
-                        node = e.ref;
-                        node_d = e.d;
-                    }
-                }
-                have = false;
-                if (active && !(node_d > best))
-                {
-                    const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
-                    const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
-                    const float Lmin = box_mindist(lp, q), Rmin = box_mindist(rp, q);
-                    const float Lmm = box_minmaxdist(lp, q), Rmm = box_minmaxdist(rp, q);
-                    bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
-                    if (Restricted)
-                    {
-                        goL = goL && box_mindist(n.le, q) <= thrW;
-                        goR = goR && box_mindist(n.re, q) <= thrW;
-                    }
-#pragma unroll
-                    for (int side = 0; side < 2; ++side)
-                    {
-                        const uint32_t ref = side == 0 ? n.lref : n.rref;
-                        if ((side == 0 ? goL : goR) && (ref & kLeafFlag))
-                        {
-                            const uint32_t pos = ref & ~kLeafFlag;
-                            float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
-                            d *= d;
-                            if (d <= best)
-                            {
-                                best = d;
-                                win = pos;
-                            }
-                        }
-                    }
-                    const bool inL = goL && !(n.lref & kLeafFlag), inR = goR && !(n.rref & kLeafFlag);
-                    if (inL && inR)
-                        st.push(n.lref, Lmin); // R would be pushed last and popped next: keep it in registers
-                    if (inR)
-                    {
-                        node = n.rref;
-                        node_d = Rmin;
-                        have = true;
-                    }
-                    else if (inL)
-                    {
-                        node = n.lref;
-                        node_d = Lmin;
-                        have = true;
-                    }
-                }
-            }
-        }
-        if (valid)
-        {
-            leaf_pos = win;
-            dist = dm_sqrt(best);
-        }
-    }
-    template <int D>
-    WOST_DEV void query_nearest_ref(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid = true)
-    {
-        query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist, valid);
-    }
-
-    // ---------------------------------------------------------------- closest primitive, B200 traversal order
-    // Same RESULT as query_nearest_ref (index and distance bit for bit), ~5x fewer node visits on curve-like meshes.
-    // Pass 1 finds the minimum with an order the reference does not use:
+    // The closest-point traversal is RESUMABLE: nearest_begin() sets up the per-lane state, nearest_trip() opens one
+    // node or evaluates one leaf, and the caller owns the loop. Two kinds of callers:
+    //   * query_nearest / query_nearest_ref: warp-synchronous drivers, `while (__any_sync(full, active)) trip();`
+    //     -- the warp reconverges once per trip instead of wherever the compiler would place the reconvergence point of
+    //     a per-thread loop (a divergent `continue` left 4-8 of 32 lanes active, profiles/r1_notes.md);
+    //   * the persistent walk kernel (integrator.cu): lanes whose query has finished run the rest of their walk step
+    //     and start the next query while the other lanes keep traversing.
+    //
+    // Phase 1 = the reference's visit order (core/query.cuh:238-318): L handled before R, leaf children evaluated at
+    // once, internal children pushed L then R (R popped first); "<=" keeps the last visited of exact ties; a popped
+    // node is skipped when its padded mindist exceeds the running best. With thrW < inf it is "restricted": children
+    // whose EXACT-extent mindist exceeds thrW are skipped too -- the second pass of the B200 order, see below.
+    //
+    // Phase 0 = the B200 order. Same RESULT as phase 1 alone (index and distance bit for bit), ~5x fewer visits on
+    // curve-like meshes. It finds the minimum with an order the reference does not use:
     //   * the reference's sibling rule "mindist(child) <= minmaxdist(sibling)" (query.cuh:279,299) is evaluated on the
     //     rebuilt padded boxes exactly as the reference does -- it is local to a node, hence independent of visit order,
     //     and it defines the candidate set S of leaves the reference can ever reach;
@@ -417,150 +313,271 @@ namespace wost
     //     |coordinate| (>= 16 ulp) covers the rounding of the leaf distance itself, so no (near-)minimal leaf is dropped;
     //   * the sqrt + re-square of the reference (dist = length(..); dist *= dist) is only done for leaves whose squared
     //     length can still win (x -> fl(fl(sqrt x)^2) is monotone and within 3 ulp of x);
-    //   * one stack entry type for nodes and leaves: per loop trip a lane either opens a node or evaluates a leaf.
+    //   * one stack entry type for nodes and leaves: per trip a lane either opens a node or evaluates a leaf.
     // Which leaf the reference returns among EXACT ties (shared vertices / edges):
     //   * 2D (boxes padded by 1e-3, scene.cuh:12): the reference's pop-time test can never drop a tied minimum, so it
     //     returns the last visited one of its static order == the highest leaf_rank. No second pass.
     //   * 3D (boxes padded by one float epsilon, aabb.cuh:21-50): the pop-time test compares the padded mindist with
-    //     the re-squared best and drops tied / 1-ulp-near minima depending on visit order. Whenever pass 1 saw more than
-    //     one leaf within 8 ulp of the minimum, pass 2 re-walks just those subtrees in the reference's order
-    //     (query_nearest_ref_impl<Restricted>) and takes its answer.
-    //   * far field (|q| beyond ~1000x the mesh, where fp32 collapses all distances): the reference order itself.
+    //     the re-squared best and drops tied / 1-ulp-near minima depending on visit order. Whenever phase 0 saw more
+    //     than one leaf within 8 ulp of the minimum, the lane continues in phase 1 restricted to thrW = the final
+    //     pruning threshold: only the subtrees holding the (near-)tied minima are re-walked, in the reference's order.
+    //   * far field (|q| beyond ~1000x the mesh, where fp32 collapses all distances): phase 1 from the start.
+    constexpr uint32_t kFullMask = 0xffffffffu;
+
     template <int D>
-    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid = true)
+    struct NearestTrav
     {
-        if (bvh.nprims <= 1)
+        uint32_t cur;   // phase 0: node or leaf ref to process; phase 1: node to open (kInvalid: pop first)
+        float cur_d;    // phase 0: exact-extent mindist of cur; phase 1: padded mindist of cur
+        float best;     // re-squared distance of the winner, as the reference keeps it
+        float thr;      // phase 0: (sqrt(best) + slack)^2; phase 1: thrW
+        float slack;
+        uint32_t win;   // leaf position of the winner
+        uint32_t best_rank;
+        int n_near;     // 3D: leaves seen within 8 ulp of the running minimum
+        int phase;
+        bool have_rank;
+    };
+
+    template <int D>
+    WOST_DEV void nearest_enter_phase1(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t, float thrW)
+    {
+        t.phase = 1;
+        t.win = kInvalid;
+        t.best = dm_inf();
+        t.thr = thrW;
+        t.cur = 0;
+        t.cur_d = box_mindist(root_box_of(bvh), q);
+        st.sp = 0;
+    }
+    // -> true when trips are needed; false when the result is already in t (0 or 1 primitives)
+    template <int D, bool RefOrder>
+    WOST_DEV bool nearest_begin(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
+    {
+        t.win = kInvalid;
+        t.best = dm_inf();
+        t.phase = 0;
+        if (bvh.nprims <= 0)
+            return false;
+        if (bvh.nprims == 1)
         {
-            query_nearest_ref_impl<D, false>(bvh, q, st, 0.0f, leaf_pos, dist, valid);
-            return;
+            const float d = prim_distance(load_prim(bvh.leaf_prim), q);
+            t.win = 0;
+            t.best = d * d;
+            return false;
+        }
+        if (RefOrder)
+        {
+            nearest_enter_phase1(bvh, q, st, t, dm_inf());
+            return true;
         }
         float qmax = 0.0f;
 #pragma unroll
         for (int k = 0; k < D; ++k)
             qmax = fmax_nn(qmax, dm_abs(q[k]));
-        const bool far = qmax > 1024.0f * bvh.max_abs_coord || (D == 2 && qmax > 2000.0f);
-        const float slack = fmax_nn(qmax, bvh.max_abs_coord) * 1.9073486328125e-06f; // 2^-19
-        uint32_t win = kInvalid;
-        float best = dm_inf(); // re-squared distance of the winner, as the reference keeps it
-        float thr = dm_inf();  // (sqrt(best) + slack)^2
-        uint32_t best_rank = 0;
-        bool have_rank = false;
-        int n_near = 0; // leaves seen within 8 ulp of the running minimum (3D tie detection)
+        if (qmax > 1024.0f * bvh.max_abs_coord || (D == 2 && qmax > 2000.0f))
+        {
+            nearest_enter_phase1(bvh, q, st, t, dm_inf());
+            return true;
+        }
+        t.slack = fmax_nn(qmax, bvh.max_abs_coord) * 1.9073486328125e-06f; // 2^-19
+        t.thr = dm_inf();
+        t.best_rank = 0;
+        t.have_rank = false;
+        t.n_near = 0;
+        t.cur = 0;
+        t.cur_d = 0.0f;
         st.sp = 0;
-        uint32_t cur = 0;
-        float cur_d = 0.0f;
-        bool active = valid && !far;
+        return true;
+    }
+    template <int D>
+    WOST_DEV float nearest_distance(const NearestTrav<D> &t) { return dm_sqrt(t.best); }
+
+    // one trip of phase 1 -> still active
+    template <int D, bool RefOrder>
+    WOST_DEV bool nearest_trip_ref(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
+    {
+        if (t.cur == kInvalid)
+        {
+            if (st.empty())
+                return false;
+            const StackEntry e = st.pop();
+            t.cur = e.ref;
+            t.cur_d = e.d;
+        }
+        const uint32_t node = t.cur;
+        t.cur = kInvalid;
+        if (t.cur_d > t.best)
+            return true;
+        const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
+        const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
+        const float Lmin = box_mindist(lp, q), Rmin = box_mindist(rp, q);
+        const float Lmm = box_minmaxdist(lp, q), Rmm = box_minmaxdist(rp, q);
+        bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
+        if (!RefOrder)
+        {
+            goL = goL && box_mindist(n.le, q) <= t.thr;
+            goR = goR && box_mindist(n.re, q) <= t.thr;
+        }
+#pragma unroll
+        for (int side = 0; side < 2; ++side)
+        {
+            const uint32_t ref = side == 0 ? n.lref : n.rref;
+            if ((side == 0 ? goL : goR) && (ref & kLeafFlag))
+            {
+                const uint32_t pos = ref & ~kLeafFlag;
+                float d = prim_distance(load_prim(bvh.leaf_prim + pos), q);
+                d *= d;
+                if (d <= t.best)
+                {
+                    t.best = d;
+                    t.win = pos;
+                }
+            }
+        }
+        const bool inL = goL && !(n.lref & kLeafFlag), inR = goR && !(n.rref & kLeafFlag);
+        if (inL && inR)
+            st.push(n.lref, Lmin); // R would be pushed last and popped next: keep it in registers
+        if (inR)
+        {
+            t.cur = n.rref;
+            t.cur_d = Rmin;
+        }
+        else if (inL)
+        {
+            t.cur = n.lref;
+            t.cur_d = Lmin;
+        }
+        return true;
+    }
+
+    // one trip -> still active
+    template <int D, bool RefOrder>
+    WOST_DEV bool nearest_trip(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
+    {
+        if (RefOrder || t.phase == 1)
+            return nearest_trip_ref<D, RefOrder>(bvh, q, st, t);
+        bool have = false;
+        if (t.cur & kLeafFlag)
+        {
+            if (t.cur_d <= t.thr)
+            {
+                const uint32_t pos = t.cur & ~kLeafFlag;
+                const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
+                if (d2 <= t.best * 1.000002f)
+                {
+                    const float d = dm_sqrt(d2);
+                    const float g = d * d;
+                    bool take = g < t.best;
+                    if (D == 3)
+                    {
+                        if (take)
+                            t.n_near = (t.best <= g * 1.000001f) ? t.n_near + 1 : 1;
+                        else if (g <= t.best * 1.000001f)
+                            ++t.n_near;
+                    }
+                    if (take)
+                        t.have_rank = false;
+                    else if (D == 2 && g == t.best && t.win != kInvalid)
+                    {
+                        // exact tie: the reference keeps the last visited leaf of its own (static) order
+                        const uint32_t rk = __ldg(bvh.leaf_rank + pos);
+                        if (!t.have_rank)
+                        {
+                            t.best_rank = __ldg(bvh.leaf_rank + t.win);
+                            t.have_rank = true;
+                        }
+                        take = rk > t.best_rank;
+                        if (take)
+                            t.best_rank = rk;
+                    }
+                    if (take)
+                    {
+                        t.best = g;
+                        t.win = pos;
+                        const float u = d + t.slack;
+                        t.thr = u * u;
+                    }
+                }
+            }
+        }
+        else
+        {
+            const NodeViewE<D> n = load_tnode_e(bvh.tnodes + t.cur);
+            const float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
+            bool goL = Le <= t.thr, goR = Re <= t.thr;
+            if (goL || goR)
+            {
+                const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
+                if (goL)
+                    goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
+                if (goR)
+                    goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
+                if (goL && goR)
+                {
+                    const bool lnear = Le <= Re;
+                    st.push(lnear ? n.rref : n.lref, lnear ? Re : Le);
+                    t.cur = lnear ? n.lref : n.rref;
+                    t.cur_d = lnear ? Le : Re;
+                    have = true;
+                }
+                else if (goL || goR)
+                {
+                    t.cur = goL ? n.lref : n.rref;
+                    t.cur_d = goL ? Le : Re;
+                    have = true;
+                }
+            }
+        }
+        if (have)
+            return true;
+        while (!st.empty())
+        {
+            const StackEntry e = st.pop();
+            if (e.d <= t.thr)
+            {
+                t.cur = e.ref;
+                t.cur_d = e.d;
+                return true;
+            }
+        }
+        if (D == 3 && t.n_near > 1)
+        {
+            nearest_enter_phase1(bvh, q, st, t, t.thr);
+            return true;
+        }
+        return false;
+    }
+
+    // Warp-synchronous drivers: the 32 lanes of a warp call these together; lanes without a query pass valid = false.
+    // Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]) and the distance.
+    template <int D, bool RefOrder>
+    WOST_DEV void query_nearest_sync(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid)
+    {
+        NearestTrav<D> t;
+        bool active = false;
+        if (valid)
+            active = nearest_begin<D, RefOrder>(bvh, q, st, t);
         while (__any_sync(kFullMask, active))
         {
             if (active)
-            {
-                bool have = false;
-                if (cur & kLeafFlag)
-                {
-                    if (cur_d <= thr)
-                    {
-                        const uint32_t pos = cur & ~kLeafFlag;
-                        const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
-                        if (d2 <= best * 1.000002f)
-                        {
-                            const float d = dm_sqrt(d2);
-                            const float g = d * d;
-                            bool take = g < best;
-                            if (D == 3)
-                            {
-                                if (take)
-                                    n_near = (best <= g * 1.000001f) ? n_near + 1 : 1;
-                                else if (g <= best * 1.000001f)
-                                    ++n_near;
-                            }
-                            if (take)
-                                have_rank = false;
-                            else if (D == 2 && g == best && win != kInvalid)
-                            {
-                                // exact tie: the reference keeps the last visited leaf of its own (static) order
-                                const uint32_t rk = __ldg(bvh.leaf_rank + pos);
-                                if (!have_rank)
-                                {
-                                    best_rank = __ldg(bvh.leaf_rank + win);
-                                    have_rank = true;
-                                }
-                                take = rk > best_rank;
-                                if (take)
-                                    best_rank = rk;
-                            }
-                            if (take)
-                            {
-                                best = g;
-                                win = pos;
-                                const float t = d + slack;
-                                thr = t * t;
-                            }
-                        }
-                    }
-                }
-                else
-                {
-                    const NodeViewE<D> n = load_tnode_e(bvh.tnodes + cur);
-                    const float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
-                    bool goL = Le <= thr, goR = Re <= thr;
-                    if (goL || goR)
-                    {
-                        const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
-                        if (goL)
-                            goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
-                        if (goR)
-                            goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
-                        if (goL && goR)
-                        {
-                            const bool lnear = Le <= Re;
-                            st.push(lnear ? n.rref : n.lref, lnear ? Re : Le);
-                            cur = lnear ? n.lref : n.rref;
-                            cur_d = lnear ? Le : Re;
-                            have = true;
-                        }
-                        else if (goL || goR)
-                        {
-                            cur = goL ? n.lref : n.rref;
-                            cur_d = goL ? Le : Re;
-                            have = true;
-                        }
-                    }
-                }
-                if (!have)
-                {
-                    active = false;
-                    while (!st.empty())
-                    {
-                        const StackEntry e = st.pop();
-                        if (e.d <= thr)
-                        {
-                            cur = e.ref;
-                            cur_d = e.d;
-                            active = true;
-                            break;
-                        }
-                    }
-                }
-            }
-        }
-        const bool pass2 = valid && (far || (D == 3 && n_near > 1));
-        if (__any_sync(kFullMask, pass2))
-        {
-            uint32_t win2 = kInvalid;
-            float dist2 = 0.0f;
-            query_nearest_ref_impl<D, true>(bvh, q, st, far ? dm_inf() : thr, win2, dist2, pass2);
-            if (pass2)
-            {
-                leaf_pos = win2;
-                dist = dist2;
-                return;
-            }
+                active = nearest_trip<D, RefOrder>(bvh, q, st, t);
         }
         if (valid)
         {
-            leaf_pos = win;
-            dist = dm_sqrt(best);
+            leaf_pos = t.win;
+            dist = nearest_distance(t);
         }
+    }
+    template <int D>
+    WOST_DEV void query_nearest(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid = true)
+    {
+        query_nearest_sync<D, false>(bvh, q, st, leaf_pos, dist, valid);
+    }
+    template <int D>
+    WOST_DEV void query_nearest_ref(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid = true)
+    {
+        query_nearest_sync<D, true>(bvh, q, st, leaf_pos, dist, valid);
     }
 
     // ---------------------------------------------------------------- closest silhouette (core/query.cuh:325-423)

@@ -293,23 +293,14 @@ namespace wost
 
     // ---------------------------------------------------------------------------------------------------------
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
-    // RefOrder: closest-point queries visit the tree in the reference's own order (query_nearest_ref) -- same results,
-    // kept as the on-device stand-in for the reference's traversal cost (bench.py --walk-mode reforder).
-    template <int D, bool RefOrder>
-    WOST_DEV bool walk_step_uniform(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc, bool valid)
+    // Everything of a walk step that follows the closest-point query on the Dirichlet mesh (R_D, leaf position pos).
+    template <int D>
+    WOST_DEV bool walk_step_tail(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc, float R_D, uint32_t pos)
     {
         const float eps = c.eps;
         // ---- separate (integrator/uniform/integrator.cu:102-212)
-        float R_D = dm_inf();
         if (c.dir.nprims > 0)
         {
-            uint32_t pos = kInvalid;
-            if (RefOrder)
-                query_nearest_ref(c.dir, w.x, st, pos, R_D, valid);
-            else
-                query_nearest(c.dir, w.x, st, pos, R_D, valid);
-            if (!valid)
-                return false;
             if (R_D < eps)
             {
                 const Prim<D> pr = load_prim(c.dir.leaf_prim + pos);
@@ -331,8 +322,6 @@ namespace wost
                 }
             }
         }
-        if (!valid)
-            return false;
         float R_N = dm_inf();
         if (c.neu.nprims > 0)
             R_N = query_silhouette(c.neu, w.x, false, st);
@@ -500,5 +489,20 @@ namespace wost
             w.nN = normal;
         }
         return true;
+    }
+    // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
+    // Warp-synchronous (the closest-point driver is): every lane of the warp calls it, lanes without a walk pass valid = false.
+    // RefOrder: closest-point queries visit the tree in the reference's own order -- same results, kept as the
+    // on-device stand-in for the reference's traversal cost (bench.py --walk-mode reforder).
+    template <int D, bool RefOrder>
+    WOST_DEV bool walk_step_uniform(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc, bool valid)
+    {
+        float R_D = dm_inf();
+        uint32_t pos = kInvalid;
+        if (c.dir.nprims > 0)
+            query_nearest_sync<D, RefOrder>(c.dir, w.x, st, pos, R_D, valid);
+        if (!valid)
+            return false;
+        return walk_step_tail<D>(c, w, depth, st, acc, R_D, pos);
     }
 } // namespace wost

@@ -115,9 +115,12 @@ extern "C"
     } wost_channel;
     typedef enum wost_walk_mode
     {
-        WOST_MODE_WAVEFRONT = 0,      /* one fused kernel per bounce over compacted SoA queues */
-        WOST_MODE_REFERENCE_ORDER = 2 /* same kernel, closest-point queries in the reference's visit order (core/query.cuh:238-318):
-                                         identical results; the on-device stand-in for the reference's traversal cost */
+        WOST_MODE_DEFAULT = 0,        /* = WOST_MODE_PERSISTENT */
+        WOST_MODE_PERSISTENT = 1,     /* register-resident walks: persistent lanes pull (pixel, sample) jobs, one launch per spp batch */
+        WOST_MODE_REFERENCE_ORDER = 2, /* wavefront kernel, closest-point queries in the reference's visit order (core/query.cuh:238-318):
+                                          identical results; the on-device stand-in for the reference's traversal cost */
+        WOST_MODE_WAVEFRONT = 3,      /* one fused kernel per bounce over compacted SoA queues */
+        WOST_MODE_PERSISTENT_REFERENCE_ORDER = 4 /* persistent kernel with the reference's visit order */
     } wost_walk_mode;
 
     typedef struct wost_settings /* IntegratorSettings: integrator/uniform/integrator.h:28-49, guided/integrator.h:56-90 */
