@@ -327,6 +327,13 @@ def main():
     bps = BYTES_PER_STEP[args.workload]
     achieved = steps_total * bps / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
 
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic_r1.json")))
+        if tj.get("kernel", "").split("<")[0] in ("k_walk_persistent" if args.walk_mode.startswith("persistent") else "k_step_uniform") and dim == 2:
+            traffic = tj["dram_bytes_per_walk_step"] * steps_total / max(1, kern_launches)  # DRAM bytes per launch, from the committed ncu capture
+    except Exception:
+        pass
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, cores, sample, _, _ = cpu_oracle_sample(wl)
@@ -343,7 +350,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e,
                     "path": "wost_scene_create+LBVH build -> wost_problem_create -> wost_integrator_create -> wost_solve -> wost_film_download"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "kernel": ("k_walk_persistent<%d>" if args.walk_mode.startswith("persistent") else "k_step_uniform<%d>") % dim, "bytes_per_walk_step": bps, "launches": int(kern_launches),
                          "avg_launch_ms": kern_ms / max(1, kern_launches), "kernel_share_of_step": kern_ms_max / dev_ms if dev_ms > 0 else None,
                          "peak_source": peak_src},

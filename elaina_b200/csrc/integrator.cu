@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 
 namespace wost
@@ -157,7 +158,7 @@ namespace wost
     // number of visits per query varies 10x between neighbouring lanes, and a bounce costs neither a kernel launch nor a
     // queue round trip through HBM. Same Philox stream (pixel, sample, depth) and same per-(slot, pixel) accumulators
     // as the wavefront kernel, hence the same film bit for bit.
-    constexpr int kRefillThreshold = 8;
+    constexpr int kRefillThreshold = 6;
 
     struct PersistArgs
     {
@@ -168,6 +169,7 @@ namespace wost
         float4 *acc; // [slot][pixel]
         int npix;
         int max_depth;
+        int refill_threshold;
         int *cursor;
         unsigned long long *steps;
         int *overflow;
@@ -196,7 +198,7 @@ namespace wost
         {
             const unsigned trav_mask = __ballot_sync(kFullMask, trav);
             const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has_walk || !exhausted));
-            if (pend_mask != 0u && (__popc(pend_mask) >= kRefillThreshold || trav_mask == 0u))
+            if (pend_mask != 0u && (__popc(pend_mask) >= a.refill_threshold || trav_mask == 0u))
             {
                 if (!trav && has_walk)
                 {
@@ -439,6 +441,9 @@ namespace wost
         int occ = 1;
         WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_walk_persistent<D, RefOrder>, kWalkBlock, smem));
         const int grid_full = sm_count() * std::max(1, occ);
+        int refill_threshold = kRefillThreshold;
+        if (const char *e = getenv("WOST_REFILL_THRESHOLD")) // tuning knob (profiles/r1_notes.md)
+            refill_threshold = std::max(1, std::min(32, atoi(e)));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0;
@@ -464,6 +469,7 @@ namespace wost
             a.acc = it->d_acc.ptr;
             a.npix = it->npix;
             a.max_depth = it->s.max_walking_depth;
+            a.refill_threshold = refill_threshold;
             a.cursor = it->d_counts.ptr;
             a.steps = it->d_steps.ptr;
             a.overflow = it->d_overflow.ptr;
