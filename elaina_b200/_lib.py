@@ -66,6 +66,11 @@ class Settings(ctypes.Structure):
         ("pixel_stride_rows", c_int),
         ("num_shards", c_int),
         ("shard", c_int),
+        ("mlp_impl", c_int),
+        ("max_train_depth", c_int),
+        ("train_batch_size", c_int),
+        ("train_min_batch", c_int),
+        ("train_batches_per_frame", c_int),
     ]
 
 
@@ -99,7 +104,19 @@ SYMBOLS = [
     ("wost_film_device_ptr", c_int, [c_void_p, c_int, _PP(c_void_p)]),
     ("wost_last_launch_count", c_int, [c_void_p, _PP(c_u64)]),
     ("wost_last_step_kernel_time", c_int, [c_void_p, _PP(c_u64), _PP(c_float)]),
+    ("wost_reset_network", c_int, [c_void_p, c_char_p]),
+    ("wost_reset_training", c_int, [c_void_p]),
+    ("wost_query_network", c_int, [c_void_p, c_void_p, c_void_p]),
+    ("wost_guided_network_info", c_int, [c_void_p, _PP(c_int), _PP(c_int), _PP(c_int)]),
+    ("wost_guided_get_params", c_int, [c_void_p, c_int, c_void_p]),
+    ("wost_guided_set_params", c_int, [c_void_p, c_void_p]),
+    ("wost_guided_infer", c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    ("wost_guided_train_batch", c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PP(c_float), c_void_p]),
+    ("wost_vmm_eval", c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_u32, c_void_p, c_void_p, c_void_p]),
+    ("wost_set_allreduce", c_int, [c_void_p, c_void_p, c_void_p]),
+    ("wost_guided_last_stats", c_int, [c_void_p, _PP(c_u64), _PP(c_u64), _PP(c_float)]),
 ]
+ALLREDUCE_FN = ctypes.CFUNCTYPE(c_int, c_void_p, c_void_p, c_u64, c_void_p)
 
 _lib = None
 

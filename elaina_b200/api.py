@@ -201,7 +201,8 @@ class Problem:
 def make_settings(frame_size=(1024, 1024), max_walking_depth=64, samples_per_pixel=1, epsilon_shell=1.0, seed=0,
                   spp_batch=0, walk_mode=0, pixel_begin=0, pixel_end=0, pixel_stride_rows=0, num_shards=1, shard=0,
                   train_spp_count=0, max_guided_depth_training=0, max_guided_depth_guiding=0,
-                  uniform_fraction_training=1.0, uniform_fraction_guiding=1.0, debug_pixel=0):
+                  uniform_fraction_training=1.0, uniform_fraction_guiding=1.0, debug_pixel=0,
+                  mlp_impl=0, max_train_depth=0, train_batch_size=0, train_min_batch=0, train_batches_per_frame=0):
     s = Settings()
     s.frame_w, s.frame_h = int(frame_size[0]), int(frame_size[1])
     s.max_walking_depth, s.samples_per_pixel = int(max_walking_depth), int(samples_per_pixel)
@@ -214,6 +215,8 @@ def make_settings(frame_size=(1024, 1024), max_walking_depth=64, samples_per_pix
     s.seed, s.walk_mode, s.spp_batch = int(seed), int(walk_mode), int(spp_batch)
     s.pixel_begin, s.pixel_end = int(pixel_begin), int(pixel_end)
     s.pixel_stride_rows, s.num_shards, s.shard = int(pixel_stride_rows), int(num_shards), int(shard)
+    s.mlp_impl, s.max_train_depth = int(mlp_impl), int(max_train_depth)
+    s.train_batch_size, s.train_min_batch, s.train_batches_per_frame = int(train_batch_size), int(train_min_batch), int(train_batches_per_frame)
     return s
 
 
@@ -290,3 +293,132 @@ class _Integrator:
 
 class UniformIntegrator(_Integrator):
     kind = UNIFORM
+
+
+def settings_from_json(setting, **extra):
+    """IntegratorSettings / GuidedIntegratorSettings JSON block (integrator/uniform/integrator.h:39-48,
+    integrator/guided/integrator.h:75-89) -> Settings. All reference keys are required, like the reference's
+    NLOHMANN_DEFINE_TYPE_INTRUSIVE deserialisation; guided keys only when present."""
+    kw = dict(frame_size=tuple(setting["frameSize"]), max_walking_depth=setting["maxWalkingDepth"],
+              samples_per_pixel=setting["samplesPerPixel"], epsilon_shell=setting["epsilonShell"],
+              debug_pixel=setting.get("debugPixel", 0))
+    if "trainSppCount" in setting:
+        kw.update(train_spp_count=setting["trainSppCount"],
+                  max_guided_depth_training=setting["maxGuidedDepthInTrainingPhase"],
+                  max_guided_depth_guiding=setting["maxGuidedDepthInGuidingPhase"],
+                  uniform_fraction_training=setting["uniformFractionInTrainingPhase"],
+                  uniform_fraction_guiding=setting["uniformFractionInGuidingPhase"])
+    kw.update(extra)
+    s = make_settings(**kw)
+    for key, attr in (("saveSppMetricsDuration", "save_spp_metrics_duration"), ("saveSppMetricsUntil", "save_spp_metrics_until"),
+                      ("saveTimeMetricsDuration", "save_time_metrics_duration")):
+        if key in setting:
+            setattr(s, attr, int(setting[key]))
+    return s
+
+
+DEFAULT_NETWORK = {  # the "network" block of data/ladybug/n.json:49-81
+    "encoding": {"otype": "DenseGrid", "n_levels": 8, "n_features_per_level": 4, "base_resolution": 8,
+                 "per_level_scale": 1.4049999713897705, "interpolation": "Linear"},
+    "loss": {"otype": "L2"},
+    "network": {"otype": "FullyFusedMLP", "activation": "ReLU", "output_activation": "None", "n_neurons": 64, "n_hidden_layers": 3},
+    "optimizer": {"otype": "Ema", "decay": 0.95, "nested": {"otype": "Adam", "learning_rate": 8e-3, "beta1": 0.9, "beta2": 0.99,
+                                                           "epsilon": 1e-15, "l2_reg": 1e-6, "adabound": False}},
+}
+
+
+class GuidedIntegrator(_Integrator):
+    """GuidedIntegrator<DIM> (integrator/guided/integrator.h:95-253): solve() trains the guiding network for
+    trainSppCount samples per pixel, then keeps guiding with the learned mixture."""
+    kind = GUIDED
+
+    def __init__(self, problem, settings, network=None):
+        super().__init__(problem, settings)
+        self.dim = problem.dim
+        self._cb = None
+        self.resetNetwork(network if network is not None else DEFAULT_NETWORK)
+
+    def resetNetwork(self, config):
+        text = config if isinstance(config, str) else json.dumps(config)
+        check(_lib.load().wost_reset_network(self.h, text.encode()))
+        n, m, k = c_int(), c_int(), c_int()
+        check(_lib.load().wost_guided_network_info(self.h, ctypes.byref(n), ctypes.byref(m), ctypes.byref(k)))
+        self.n_params, self.n_mlp_params, self.encoded_width = n.value, m.value, k.value
+
+    def resetTraining(self):
+        check(_lib.load().wost_reset_training(self.h))
+
+    def queryNetwork(self, p):
+        p = np.ascontiguousarray(p, np.float32).reshape(self.dim)
+        out = np.zeros(8 * (self.dim + 2) + 1, np.float32)
+        check(_lib.load().wost_query_network(self.h, _p(p), _p(out)))
+        return out
+
+    def get_params(self, inference=False):
+        out = np.zeros(self.n_params, np.float32)
+        check(_lib.load().wost_guided_get_params(self.h, 1 if inference else 0, _p(out)))
+        return out
+
+    def set_params(self, params):
+        params = np.ascontiguousarray(params, np.float32)
+        assert len(params) == self.n_params
+        check(_lib.load().wost_guided_set_params(self.h, _p(params)))
+
+    def infer(self, pts, impl=0, inference_weights=True):
+        """raw network outputs (n, 48) at world-space points; impl 0 = tcgen05 tile kernel, 1 = SIMT kernel"""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, self.dim)
+        out = np.zeros((len(pts), 48), np.float32)
+        check(_lib.load().wost_guided_infer(self.h, _p(pts), len(pts), int(impl), 1 if inference_weights else 0, _p(out)))
+        return out
+
+    def train_batch(self, pos, dirs, nrm, dir_pdf, li, on_neumann, want_grad=True):
+        """one optimiser step on explicit samples -> (mean loss, loss-scaled gradient slab | None)"""
+        d = self.dim
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, d)
+        dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, d)
+        nrm = np.ascontiguousarray(nrm, np.float32).reshape(-1, d)
+        dir_pdf = np.ascontiguousarray(dir_pdf, np.float32)
+        li = np.ascontiguousarray(li, np.float32)
+        on = np.ascontiguousarray(on_neumann, np.uint8)
+        grad = np.zeros(self.n_params, np.float32) if want_grad else None
+        loss = c_float()
+        check(_lib.load().wost_guided_train_batch(self.h, _p(pos), _p(dirs), _p(nrm), _p(dir_pdf), _p(li), _p(on), len(pos), ctypes.byref(loss), _p(grad)))
+        return loss.value, grad
+
+    def set_allreduce(self, fn):
+        """fn(device_ptr, n_floats, stream_ptr) -> None: enqueue a SUM all-reduce of the gradient slab on that stream"""
+        if fn is None:
+            self._cb = None
+            check(_lib.load().wost_set_allreduce(self.h, None, None))
+            return
+
+        def tramp(user, buf, n, stream):
+            try:
+                fn(buf, n, stream)
+                return 0
+            except Exception:
+                import traceback
+                traceback.print_exc()
+                return 1
+        self._cb = _lib.ALLREDUCE_FN(tramp)
+        check(_lib.load().wost_set_allreduce(self.h, ctypes.cast(self._cb, c_void_p), None))
+
+    @property
+    def train_stats(self):
+        a, b, l = c_u64(), c_u64(), c_float()
+        check(_lib.load().wost_guided_last_stats(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(l)))
+        return dict(samples=a.value, steps=b.value, loss=l.value)
+
+
+def vmm_eval(dim, raw, dirs, nrm, on_neumann, seed=0):
+    """device probe of VMM<DIM,8>: (pdf, grad wrt activated lobe params, one sampled direction per row)"""
+    raw = np.ascontiguousarray(raw, np.float32)
+    dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, dim)
+    nrm = np.ascontiguousarray(nrm, np.float32).reshape(-1, dim)
+    on = np.ascontiguousarray(on_neumann, np.uint8)
+    n = len(dirs)
+    pdf = np.zeros(n, np.float32)
+    grad = np.zeros((n, 8 * (dim + 2)), np.float32)
+    smp = np.zeros((n, dim), np.float32)
+    check(_lib.load().wost_vmm_eval(dim, _p(raw), _p(dirs), _p(nrm), _p(on), n, int(seed), _p(pdf), _p(grad), _p(smp)))
+    return pdf, grad, smp

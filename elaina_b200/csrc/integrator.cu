@@ -329,6 +329,10 @@ namespace wost
         }
     }
 
+    void launch_resolve(wost_integrator *it, int nslots, float spp)
+    {
+        k_resolve<<<div_up(it->npix, 256), 256, 0, it->stream>>>(it->npix, nslots, it->d_acc.ptr, spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
+    }
     template <int D, bool RefOrder>
     static wost_status solve_uniform(wost_integrator *it, uint64_t *walk_steps)
     {
@@ -602,9 +606,9 @@ extern "C"
             set_last_error("wost_integrator_create: invalid argument");
             return WOST_ERR_INVALID;
         }
-        if (kind != WOST_UNIFORM)
+        if (kind != WOST_UNIFORM && kind != WOST_GUIDED)
         {
-            set_last_error("wost_integrator_create: integrator kind not available in this build");
+            set_last_error("wost_integrator_create: unknown integrator kind");
             return WOST_ERR_UNSUPPORTED;
         }
         const wost_settings &s = *settings;
@@ -664,14 +668,16 @@ extern "C"
         };
         if (it->d_active.upload(active.data(), active.size()) != cudaSuccess)
             return fail("active pixel upload");
-        for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < 2 && kind == WOST_UNIFORM; ++i)
         {
             if (it->qa[i].alloc(it->queue_capacity) != cudaSuccess || it->qb[i].alloc(it->queue_capacity) != cudaSuccess)
                 return fail("queue allocation");
             if (it->dim == 3 && it->qc[i].alloc(it->queue_capacity) != cudaSuccess)
                 return fail("queue allocation");
         }
-        if (it->d_counts.alloc((size_t)2 * (s.max_walking_depth + 1)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
+        if (kind == WOST_GUIDED && guided_alloc(it) != WOST_OK)
+            return fail("guided buffer allocation");
+        if (it->d_counts.alloc((size_t)2 * (s.max_walking_depth + 2)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
             it->d_acc.alloc((size_t)S * it->npix) != cudaSuccess || it->d_overflow.alloc(1) != cudaSuccess)
             return fail("buffer allocation");
         for (int c = 0; c < WOST_CH_COUNT; ++c)
@@ -698,6 +704,9 @@ extern "C"
         const auto t0 = std::chrono::high_resolution_clock::now();
         WOST_CUDA_TRY(cudaEventRecord(it->ev0, it->stream));
         wost_status rc;
+        if (it->kind == WOST_GUIDED)
+            rc = solve_guided(it, walk_steps);
+        else
         switch (it->s.walk_mode)
         {
         case WOST_MODE_REFERENCE_ORDER:

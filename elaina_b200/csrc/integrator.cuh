@@ -1,5 +1,6 @@
 // Host-side integrator object behind `wost_integrator`.
 #pragma once
+#include "guided.cuh"
 #include "problem.cuh"
 
 namespace wost
@@ -41,6 +42,15 @@ struct wost_integrator
     uint64_t step_launches = 0;  // launches of the fused walk-step kernel in the last solve
     float step_kernel_ms = 0.0f; // device time between the first and last walk-step launch of every spp batch, summed
     std::vector<cudaEvent_t> batch_ev; // 2 events per spp batch
+    // guided integrator
+    std::unique_ptr<wost::GuideNet> net;
+    wost::GuidedBuffers gb;
+    wost::DevBuf<float4> gq[2][3]; // guided out-shell queues: {x,thp} {n,R_B} {pixel,sample|onN,Tr,Tg}
+    wost::DevBuf<float> gq3[2];    // Tb
+    wost_allreduce_fn allreduce = nullptr;
+    void *allreduce_user = nullptr;
+    uint64_t train_samples = 0, train_steps = 0;
+    float last_loss = 0.0f;
 
     ~wost_integrator()
     {

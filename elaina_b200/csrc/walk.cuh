@@ -257,10 +257,14 @@ namespace wost
 
     // Pixel accumulator handled like the reference's addColor (integrator/uniform/workqueue.h:25-29):
     // loaded on first use, every contribution applied in stage order, stored once at the end of the step.
-    struct PixelAcc
+    // TrackTotal: also keep the running sum of the walk's own contributions (tot) -- the guided integrator derives
+    // its training targets from it (GuidedPixelStateBuffer::recordSolution / recordSourceContribution, guided.h:46-67).
+    template <bool TrackTotal>
+    struct PixelAccT
     {
         float *ptr;
         float v[3];
+        float tot[3];
         bool loaded;
         WOST_DEV void init(float *p)
         {
@@ -269,6 +273,12 @@ namespace wost
         }
         WOST_DEV void add(float c0, float c1, float c2)
         {
+            if (TrackTotal)
+            {
+                tot[0] += c0;
+                tot[1] += c1;
+                tot[2] += c2;
+            }
             if (!loaded)
             {
                 v[0] = ptr[0];
@@ -290,12 +300,18 @@ namespace wost
             }
         }
     };
+    using PixelAcc = PixelAccT<false>;
 
     // ---------------------------------------------------------------------------------------------------------
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
     // Everything of a walk step that follows the closest-point query on the Dirichlet mesh (R_D, leaf position pos).
-    template <int D>
-    WOST_DEV bool walk_step_tail(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, PixelAcc &acc, float R_D, uint32_t pos)
+    // Stages separate -> boundary -> source sample -> Neumann sample of one step. Returns false when the walk ended
+    // (epsilon-shell hit or no star radius); otherwise R_B holds the star radius of the step.
+    // rb_scale: 0.99 in the uniform integrator (integrator/uniform/integrator.cu:193-195), 1 in the guided one
+    // (integrator/guided/integrator.cu:238-239).
+    template <int D, class Acc>
+    WOST_DEV bool walk_step_contrib(const WalkCtx<D> &c, const WalkState<D> &w, uint32_t depth, SmemStack &st, Acc &acc, float R_D, uint32_t pos,
+                                    float rb_scale, float &R_B)
     {
         const float eps = c.eps;
         // ---- separate (integrator/uniform/integrator.cu:102-212)
@@ -325,8 +341,8 @@ namespace wost
         float R_N = dm_inf();
         if (c.neu.nprims > 0)
             R_N = query_silhouette(c.neu, w.x, false, st);
-        float R_B = dm_fmax(1e-4f, dm_fmin(R_D, R_N));
-        R_B *= 0.99f;
+        R_B = dm_fmax(1e-4f, dm_fmin(R_D, R_N));
+        R_B *= rb_scale;
         if (dm_isinf(R_B))
             return false;
 
@@ -438,24 +454,35 @@ namespace wost
             }
         }
 
-        // ---- one-step walk (integrator.cu:447-526)
+        return true;
+    }
+    // uniform direction of oneStepWalk (integrator.cu:447-470): sphere, or hemisphere about the Neumann normal
+    template <int D>
+    WOST_DEV Vec<D> uniform_direction(const WalkCtx<D> &c, const WalkState<D> &w, uint32_t depth, float &pdf)
+    {
+        const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_WALK, 0);
+        if (w.onN)
         {
-            const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_WALK, 0);
-            Vec<D> cur = w.x, dir;
-            float pdf, alpha = 1.0f;
+            pdf = Dims<D>::hemi_pdf();
+            return to_world(w.nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
+        }
+        pdf = Dims<D>::sphere_pdf();
+        return sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
+    }
+    // second half of oneStepWalk (integrator.cu:472-526): move along dir by R_B or to the first Neumann hit, update thp
+    template <int D>
+    WOST_DEV void walk_advance(const WalkCtx<D> &c, WalkState<D> &w, const Vec<D> &dir, float pdf, float R_B, SmemStack &st)
+    {
+        const float eps = c.eps;
+        {
+            Vec<D> cur = w.x;
+            float alpha = 1.0f;
             if (w.onN)
             {
-                dir = to_world(w.nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
-                pdf = Dims<D>::hemi_pdf();
                 alpha = 0.5f;
 #pragma unroll
                 for (int k = 0; k < D; ++k)
                     cur[k] = cur[k] + eps * w.nN[k];
-            }
-            else
-            {
-                dir = sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
-                pdf = Dims<D>::sphere_pdf();
             }
             Vec<D> next, normal;
 #pragma unroll
@@ -488,6 +515,17 @@ namespace wost
             w.onN = hit;
             w.nN = normal;
         }
+    }
+    // Everything of a UNIFORM walk step that follows the closest-point query on the Dirichlet mesh (R_D, leaf position pos).
+    template <int D, class Acc>
+    WOST_DEV bool walk_step_tail(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, Acc &acc, float R_D, uint32_t pos, float rb_scale = 0.99f)
+    {
+        float R_B;
+        if (!walk_step_contrib<D>(c, w, depth, st, acc, R_D, pos, rb_scale, R_B))
+            return false;
+        float pdf;
+        const Vec<D> dir = uniform_direction<D>(c, w, depth, pdf);
+        walk_advance<D>(c, w, dir, pdf, R_B, st);
         return true;
     }
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).

@@ -142,6 +142,13 @@ extern "C"
         int pixel_begin, pixel_end; /* shard of the frame owned by this handle; pixel_end = 0 -> whole frame */
         int pixel_stride_rows;      /* >0: interleaved row tiles: rows r with (r / stride_rows) % num_shards == shard */
         int num_shards, shard;
+        /* guided extensions (0 = the reference's constants) */
+        int mlp_impl;                /* 0: fused tcgen05 inference inside the bounce kernel; 1: validation mode, SIMT MLP kernel
+                                        writing the raw outputs to HBM like the reference (guided/integrator.cu:528-563) */
+        int max_train_depth;         /* Guidance::maxTrainDepth, default 3 (guided/integrator.h:222), <= 4 */
+        int train_batch_size;        /* TRAIN_BATCH_SIZE 524288 (guided/parameters.h:12) */
+        int train_min_batch;         /* MIN_TRAIN_BATCH_SIZE 65536 (guided/parameters.h:13) */
+        int train_batches_per_frame; /* Guidance::batchPerFrame 5 (guided/integrator.h:223) */
     } wost_settings;
 
     typedef struct wost_integrator wost_integrator;
@@ -161,6 +168,39 @@ extern "C"
     /* launches of the fused walk-step kernel in the last solve and their summed device time (CUDA events on the
      * integrator's stream around each spp batch's run of step launches) -- the roofline numerator of bench.py */
     wost_status wost_last_step_kernel_time(wost_integrator *it, uint64_t *step_launches, float *step_kernel_ms);
+
+    /* ------------------------------------------------------------------ guided integrator: the guiding network
+     * resetNetwork(json) (integrator/guided/integrator.cu:1096-1137): `tcnn_json` is the "network" block of the
+     * configuration file ({encoding{otype DenseGrid,n_levels,n_features_per_level 4,base_resolution,per_level_scale},
+     * network{FullyFusedMLP, 64 neurons, 3 hidden layers, ReLU}, optimizer{Ema{decay, nested Adam{...}}}}). */
+    wost_status wost_reset_network(wost_integrator *it, const char *tcnn_json);
+    /* resetTraining() (integrator.cu:1139-1146): re-initialise parameters and optimiser state */
+    wost_status wost_reset_training(wost_integrator *it);
+    /* queryNetwork(p) (integrator.cu:565-615): raw network output at a world-space point, 33 (2D) / 41 (3D) floats */
+    wost_status wost_query_network(wost_integrator *it, const float *p, float *out);
+    wost_status wost_guided_network_info(wost_integrator *it, int *n_params, int *n_mlp_params, int *encoded_width);
+    /* parameter slab [W0|W1|W2|W3|grid] in fp32; which = 0 training weights, 1 EMA ("inference") weights */
+    wost_status wost_guided_get_params(wost_integrator *it, int which, float *params);
+    wost_status wost_guided_set_params(wost_integrator *it, const float *params);
+    /* parity probes. infer: raw outputs (n*48, padded) at world-space points; impl 0 = tcgen05 tile kernel, 1 = SIMT.
+     * train_batch: ONE optimiser step on the given samples (n rounded down to a multiple of 128) = forward, KL gradient
+     * (compute_dL_doutput_divergence, guided/train.h:491-553), backward, Adam + EMA; grad_out (n_params floats or NULL)
+     * receives the loss-scaled gradient slab of the step, loss the mean per-sample loss. */
+    wost_status wost_guided_infer(wost_integrator *it, const float *pts, int n, int impl, int which_weights, float *out);
+    wost_status wost_guided_train_batch(wost_integrator *it, const float *pos, const float *dir, const float *nrm, const float *dir_pdf,
+                                        const float *li, const uint8_t *on_neumann, int n, float *loss, float *grad_out);
+    /* VMM<DIM,8> probe (guided/distribution.h:136-444) evaluated on the device: pdf (n) of the mixture decoded from raw
+     * (n * (8*(dim+2)+1)) at dir (+ reflected dir when on_neumann), grad (n * 8*(dim+2)) of that pdf w.r.t. the
+     * activated lobe parameters, and one sampled direction (n*dim) drawn with Philox key (seed, i). */
+    wost_status wost_vmm_eval(int dim, const float *raw, const float *dir, const float *nrm, const uint8_t *on_neumann, int n, uint32_t seed,
+                              float *pdf, float *grad, float *sampled_dir);
+    /* Multi-GPU training: called on the integrator's stream between the backward pass and the optimiser step of every
+     * batch with the device gradient slab (n_floats floats, last word = number of ranks whose batch was valid). The
+     * callback must enqueue a SUM all-reduce on `stream` (a cudaStream_t) and return 0. */
+    typedef int (*wost_allreduce_fn)(void *user, void *d_buf, uint64_t n_floats, void *stream);
+    wost_status wost_set_allreduce(wost_integrator *it, wost_allreduce_fn fn, void *user);
+    /* counters of the last guided solve: training samples consumed, optimiser steps, mean loss of the last batch */
+    wost_status wost_guided_last_stats(wost_integrator *it, uint64_t *train_samples, uint64_t *train_steps, float *last_loss);
 
 #ifdef __cplusplus
 }

@@ -1378,6 +1378,7 @@ namespace
 }
 
 #include "wost_oracle_walk.inl"
+#include "wost_oracle_guided.inl"
 
 extern "C"
 {

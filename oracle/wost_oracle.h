@@ -80,6 +80,31 @@ extern "C"
     void orc_solve_uniform(const orc_problem_desc *p, const orc_settings *s, int pixel_begin, int pixel_end,
                            float *solution, uint64_t *steps, int nthreads);
 
+    /* ---- guided integrator (wost_oracle_guided.inl) ---- */
+    typedef struct orc_guided_settings
+    {
+        int max_guided_depth;   /* maxGuidedDepthIn{Training,Guiding}Phase */
+        float uniform_fraction; /* uniformFractionIn{Training,Guiding}Phase */
+        int max_train_depth;    /* Guidance::maxTrainDepth (3) */
+    } orc_guided_settings;
+    void *orc_net_create(int dim, int n_levels, int base_res, float per_level_scale, const float *aabb_min, const float *aabb_max);
+    void orc_net_destroy(void *net);
+    int orc_net_num_params(void *net, int *n_mlp, int *k0);
+    void orc_net_set_params(void *net, const float *params);
+    void orc_net_forward(void *net, const float *pts, int n, float *out, float *acts, uint32_t *cell_idx, float *cell_w);
+    void orc_vmm_eval(int dim, const float *raw, const float *dir, const float *nrm, const uint8_t *onN, int n, uint32_t seed, float *pdf, float *grad,
+                      float *sampled);
+    void orc_kl_grad(int dim, const float *raw48, const float *dir, const float *nrm, const uint8_t *onN, const float *dirPdf, const float *li, int n,
+                     float scale, float *dl, float *loss);
+    float orc_eval_poly_large0(float y);
+    float orc_log_bessel(float x, int order);
+    float orc_vonmises_log_pdf(float kappa, float cos_theta);
+    float orc_vonmises_pdf(float kappa, float cos_theta);
+    float orc_vonmises_dlog_dkappa(float kappa, float cos_theta);
+    float orc_vmf_pdf(float kappa, float cos_theta);
+    int orc_solve_guided(const orc_problem_desc *p, const orc_settings *s, const orc_guided_settings *g, void *net, int pixel_begin, int pixel_end,
+                         int sample0, int nsamples, float *solution, uint64_t *steps, float *samples_out, uint8_t *samples_on, int cap, int nthreads);
+
     /* evaluation point of a pixel (dim floats) */
     void orc_eval_point(const orc_problem_desc *p, const orc_settings *s, int pixel, float *out);
 

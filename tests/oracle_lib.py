@@ -65,6 +65,53 @@ class Settings(ctypes.Structure):
     ]
 
 
+class GuidedSettings(ctypes.Structure):
+    _fields_ = [("max_guided_depth", c_int), ("uniform_fraction", c_float), ("max_train_depth", c_int)]
+
+
+class OracleNet:
+    """DenseGrid + MLP of the oracle (fp32 parameter slab [W0|W1|W2|W3|grid])."""
+
+    def __init__(self, orc, dim, n_levels, base_res, per_level_scale, aabb_min, aabb_max):
+        self.orc, self.dim, self.n_levels = orc, dim, n_levels
+        lo = np.zeros(3, np.float32)
+        hi = np.ones(3, np.float32)
+        lo[:dim] = aabb_min[:dim]
+        hi[:dim] = aabb_max[:dim]
+        self.h = c_void_p(orc.lib.orc_net_create(dim, n_levels, base_res, float(per_level_scale), _p(lo), _p(hi)))
+        nm, k0 = c_int(), c_int()
+        self.n_params = orc.lib.orc_net_num_params(self.h, ctypes.byref(nm), ctypes.byref(k0))
+        self.n_mlp, self.k0 = nm.value, k0.value
+
+    def set_params(self, params):
+        params = np.ascontiguousarray(params, np.float32)
+        assert len(params) == self.n_params
+        self.params = params
+        self.orc.lib.orc_net_set_params(self.h, _p(params))
+
+    def forward(self, pts, want_acts=False, want_cells=False):
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, self.dim)
+        n = len(pts)
+        out = np.zeros((n, 48), np.float32)
+        acts = np.zeros((n, 4, 64), np.float32) if want_acts else None
+        C = 1 << self.dim
+        ci = np.zeros((n, self.n_levels, C), np.uint32) if want_cells else None
+        cw = np.zeros((n, self.n_levels, C), np.float32) if want_cells else None
+        self.orc.lib.orc_net_forward(self.h, _p(pts), n, _p(out), _p(acts), _p(ci), _p(cw))
+        return out, acts, ci, cw
+
+    def close(self):
+        if self.h:
+            self.orc.lib.orc_net_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class _GeomLib:
     """Common surface of the oracle and the host-compiled reference (prefix 'orc_' / 'ref_')."""
 
@@ -230,6 +277,92 @@ class Oracle(_GeomLib):
         self.lib.orc_solve_uniform(ctypes.byref(desc), ctypes.byref(st), pixel_begin, pixel_end, _p(sol), ctypes.byref(steps), nthreads)
         del keep
         return sol, steps.value
+
+    # ---- guided integrator (oracle/wost_oracle_guided.inl)
+    def _bind_guided(self):
+        if getattr(self, "_guided_bound", False):
+            return
+        L = self.lib
+        L.orc_net_create.restype = c_void_p
+        L.orc_net_create.argtypes = [c_int, c_int, c_int, c_float, c_void_p, c_void_p]
+        L.orc_net_destroy.argtypes = [c_void_p]
+        L.orc_net_num_params.argtypes = [c_void_p, c_void_p, c_void_p]
+        L.orc_net_set_params.argtypes = [c_void_p, c_void_p]
+        L.orc_net_forward.argtypes = [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
+        L.orc_vmm_eval.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_u32, c_void_p, c_void_p, c_void_p]
+        L.orc_kl_grad.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float, c_void_p, c_void_p]
+        for name in ("orc_eval_poly_large0",):
+            getattr(L, name).restype = c_float
+            getattr(L, name).argtypes = [c_float]
+        L.orc_log_bessel.restype = c_float
+        L.orc_log_bessel.argtypes = [c_float, c_int]
+        for name in ("orc_vonmises_log_pdf", "orc_vonmises_pdf", "orc_vonmises_dlog_dkappa", "orc_vmf_pdf"):
+            getattr(L, name).restype = c_float
+            getattr(L, name).argtypes = [c_float, c_float]
+        L.orc_solve_guided.restype = c_int
+        L.orc_solve_guided.argtypes = [ctypes.POINTER(ProblemDesc), ctypes.POINTER(Settings), ctypes.POINTER(GuidedSettings), c_void_p, c_int, c_int,
+                                       c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]
+        self._guided_bound = True
+
+    def net(self, dim, n_levels, base_res, per_level_scale, aabb_min, aabb_max):
+        self._bind_guided()
+        return OracleNet(self, dim, n_levels, base_res, per_level_scale, aabb_min, aabb_max)
+
+    def vmm_eval(self, dim, raw, dirs, nrm, on_neumann, seed=0):
+        self._bind_guided()
+        raw = np.ascontiguousarray(raw, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, dim)
+        nrm = np.ascontiguousarray(nrm, np.float32).reshape(-1, dim)
+        on = np.ascontiguousarray(on_neumann, np.uint8)
+        n = len(dirs)
+        pdf = np.zeros(n, np.float32)
+        grad = np.zeros((n, 8 * (dim + 2)), np.float32)
+        smp = np.zeros((n, dim), np.float32)
+        self.lib.orc_vmm_eval(dim, _p(raw), _p(dirs), _p(nrm), _p(on), n, seed, _p(pdf), _p(grad), _p(smp))
+        return pdf, grad, smp
+
+    def kl_grad(self, dim, raw48, dirs, nrm, on_neumann, dir_pdf, li, scale):
+        self._bind_guided()
+        raw48 = np.ascontiguousarray(raw48, np.float32).reshape(-1, 48)
+        n = len(raw48)
+        dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, dim)
+        nrm = np.ascontiguousarray(nrm, np.float32).reshape(-1, dim)
+        on = np.ascontiguousarray(on_neumann, np.uint8)
+        dir_pdf = np.ascontiguousarray(dir_pdf, np.float32)
+        li = np.ascontiguousarray(li, np.float32)
+        dl = np.zeros((n, 48), np.float32)
+        loss = np.zeros(n, np.float32)
+        self.lib.orc_kl_grad(dim, _p(raw48), _p(dirs), _p(nrm), _p(on), _p(dir_pdf), _p(li), n, float(scale), _p(dl), _p(loss))
+        return dl, loss
+
+    def solve_guided(self, problem, settings, net, max_guided_depth, uniform_fraction, max_train_depth=3, sample0=0, nsamples=None,
+                     emit_samples=False, pixel_begin=0, pixel_end=None, nthreads=0):
+        """-> (solution (npix,3) = sum of the samples' contributions / samples_per_pixel, steps, samples dict | None)"""
+        self._bind_guided()
+        desc, keep = make_problem_desc(problem)
+        st = Settings(settings["frame_w"], settings["frame_h"], settings["max_walking_depth"],
+                      settings["samples_per_pixel"], settings["epsilon_shell"], settings.get("seed", 0))
+        gs = GuidedSettings(int(max_guided_depth), float(uniform_fraction), int(max_train_depth))
+        npx = st.frame_w * st.frame_h
+        if pixel_end is None:
+            pixel_end = npx
+        if nsamples is None:
+            nsamples = st.samples_per_pixel - sample0
+        sol = np.zeros((npx, 3), np.float32)
+        steps = c_u64(0)
+        cap = 4 * npx * nsamples if emit_samples else 0
+        so = np.zeros((max(cap, 1), 11), np.float32)
+        son = np.zeros(max(cap, 1), np.uint8)
+        n = self.lib.orc_solve_guided(ctypes.byref(desc), ctypes.byref(st), ctypes.byref(gs), net.h if net is not None else None, pixel_begin, pixel_end,
+                                      sample0, nsamples, _p(sol), ctypes.byref(steps), _p(so) if emit_samples else None,
+                                      _p(son) if emit_samples else None, cap, nthreads)
+        del keep
+        samples = None
+        if emit_samples:
+            dim = problem["dim"]
+            so, son = so[:n], son[:n]
+            samples = dict(pos=so[:, 0:dim].copy(), dir=so[:, 3:3 + dim].copy(), nrm=so[:, 6:6 + dim].copy(), pdf=so[:, 9].copy(), li=so[:, 10].copy(), onN=son.copy())
+        return sol, steps.value, samples
 
     def eval_points(self, problem, settings, pixels):
         desc, keep = make_problem_desc(problem)
