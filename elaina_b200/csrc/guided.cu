@@ -837,26 +837,18 @@ namespace wost
             const int o = r & 63;
             float *g43 = r < 64 ? a.grad + off3 + o * kHidden : a.grad + off2 + o * kHidden;
             const uint32_t c43 = kColG43 + (r < 64 ? 0 : kHidden);
-            if (r >= 64 || o < kOutPad)
-            {
+            // tcgen05.ld is warp-collective (.sync.aligned): every lane loads, only the lanes that own a real row add
+            const bool own43 = r >= 64 || o < kOutPad; // rows 48..63 of the padded dW3 block are padding
 #pragma unroll
-                for (int c16 = 0; c16 < kHidden / 16; ++c16)
+            for (int c16 = 0; c16 < kHidden / 16; ++c16)
+            {
+                float v[16];
+                tc::tmem_ld16(lane_base + c43 + c16 * 16, v);
+                if (own43)
                 {
-                    float v[16];
-                    tc::tmem_ld16(lane_base + c43 + c16 * 16, v);
 #pragma unroll
                     for (int j = 0; j < 16; ++j)
                         atomicAdd(g43 + c16 * 16 + j, v[j]);
-                }
-            }
-            else
-            {
-                // rows 48..63 of the padded dW3 block: still a warp-collective tcgen05.ld (sync.aligned), results dropped
-#pragma unroll
-                for (int c16 = 0; c16 < kHidden / 16; ++c16)
-                {
-                    float v[16];
-                    tc::tmem_ld16(lane_base + c43 + c16 * 16, v);
                 }
             }
             if (r < 64)

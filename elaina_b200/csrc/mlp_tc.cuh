@@ -30,9 +30,11 @@ namespace wost
         WOST_DEV void mbar_wait(uint64_t *bar, uint32_t parity)
         {
             const uint32_t a = smem_u32(bar);
-            uint32_t done;
+            uint32_t done, spins = 0;
             do
             {
+                if (++spins > (1u << 22)) // a lost tcgen05.commit would otherwise hang the GPU: fail loudly instead
+                    __trap();
                 asm volatile(
                     "{\n\t"
                     ".reg .pred p;\n\t"
