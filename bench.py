@@ -193,6 +193,9 @@ def main():
     ap.add_argument("--spp-batch", type=int, default=0)
     ap.add_argument("--walk-mode", default="persistent", choices=["persistent", "wavefront", "reforder", "persistent-reforder"],
                     help="reforder: closest-point queries in the reference's visit order (stand-in for the reference's traversal cost)")
+    ap.add_argument("--integrator", default="uniform", choices=["uniform", "guided"],
+                    help="guided: GuidedIntegrator with the reference's n.json settings (train spp = spp/4, guided depth 10, learned selection)")
+    ap.add_argument("--mlp-impl", type=int, default=0, help="guided: 0 = fused tcgen05 bounce kernel, 1 = validation mode (SIMT MLP through HBM)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg (line carries e2e: null)")
     args = ap.parse_args()
@@ -242,7 +245,14 @@ def main():
     # strong scaling: the frame is fixed, rows are dealt to ranks in interleaved tiles of 4 rows (pixel-keyed RNG ->
     # the summed film does not depend on N)
     shard = dict(pixel_stride_rows=4, num_shards=world, shard=rank) if world > 1 else {}
-    settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=args.spp_batch, walk_mode={"persistent": 1, "reforder": 2, "wavefront": 3, "persistent-reforder": 4}[args.walk_mode], **shard)
+    guided = args.integrator == "guided"
+    gkw = {}
+    if guided:
+        # data/{ladybug,fille}/n.json: trainSppCount = spp/4, maxGuidedDepth 10 in both phases, uniformFraction 0.5 (= learned selection)
+        gkw = dict(train_spp_count=max(1, wl["spp"] // 4), max_guided_depth_training=10, max_guided_depth_guiding=10,
+                   uniform_fraction_training=0.5, uniform_fraction_guiding=0.5, mlp_impl=args.mlp_impl)
+    settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=args.spp_batch, walk_mode={"persistent": 1, "reforder": 2, "wavefront": 3, "persistent-reforder": 4}[args.walk_mode], **shard, **gkw)
+    Integrator = (lambda p, st: api.GuidedIntegrator(p, st, api.DEFAULT_NETWORK)) if guided else api.UniformIntegrator
 
     def make_problem():
         g_d = api.Scene(dim, wl["dverts"], wl["dprims"])
@@ -250,7 +260,7 @@ def main():
         return api.Problem(dim, dirichlet=g_d, neumann=g_n, **problem_kwargs(wl))
 
     prob = make_problem()
-    it = api.UniformIntegrator(prob, settings)
+    it = Integrator(prob, settings)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     film_t = None
@@ -293,7 +303,7 @@ def main():
 
     def e2e_once():
         p = make_problem()
-        i2 = api.UniformIntegrator(p, settings)
+        i2 = Integrator(p, settings)
         i2.solve()
         if world > 1:
             # final film gather: shards own disjoint rows and write zeros elsewhere -> one NCCL sum
@@ -324,13 +334,23 @@ def main():
         e2e_value = sum_over_ranks(float(e2e_steps)) / e2e_t
 
     peak, peak_src = measured_peak()
-    bps = BYTES_PER_STEP[args.workload]
+    bps = BYTES_PER_STEP[args.workload] + (176 if guided else 0)  # + 12 B network input and 164 B output per guided step
+    relmse = None
+    if rank == 0 and world == 1 and args.workload.startswith("c3"):
+        # relMSE against the analytic field Re(z^3) over the evaluated pixels (BASELINE metric, second half)
+        from elaina_b200 import scenes as _sc
+        g = 1.5 * (2.0 * np.arange(W, dtype=np.float64) / W - 1.0)
+        X, Y = np.meshgrid(g, g)
+        ref = _sc.harmonic_2d(np.stack([X, Y], -1), 3)
+        sol = it.film()[..., 0].astype(np.float64)
+        m = wl["mask"].astype(bool)
+        relmse = float(np.mean((sol[m] - ref[m]) ** 2 / (ref[m] ** 2 + 1e-2)))
     achieved = steps_total * bps / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
 
     traffic = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic_r1.json")))
-        if tj.get("kernel", "").split("<")[0] in ("k_walk_persistent" if args.walk_mode.startswith("persistent") else "k_step_uniform") and dim == 2:
+        if not guided and tj.get("kernel", "").split("<")[0] in ("k_walk_persistent" if args.walk_mode.startswith("persistent") else "k_step_uniform") and dim == 2:
             traffic = tj["dram_bytes_per_walk_step"] * steps_total / max(1, kern_launches)  # DRAM bytes per launch, from the committed ncu capture
     except Exception:
         pass
@@ -344,18 +364,20 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": wl["desc"], "integrator": "uniform", "walk_mode": args.walk_mode, "spp_batch": args.spp_batch or "auto (~16M walks in flight)",
+            "config": {"workload": wl["desc"], "integrator": args.integrator, "walk_mode": args.walk_mode if not guided else ("fused tcgen05 bounce kernel" if args.mlp_impl == 0 else "validation: SIMT MLP through HBM"), "relmse_vs_analytic": relmse, "spp_batch": args.spp_batch or "auto (~16M walks in flight)",
                        "walk_steps_per_step": steps_all / args.steps, "sharding": "interleaved 4-row tiles over %d ranks" % world,
                        "l2": "256 MiB flush between timed steps; live working set (queues + accumulators, >1 GB) exceeds the 126 MB L2"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e,
                     "path": "wost_scene_create+LBVH build -> wost_problem_create -> wost_integrator_create -> wost_solve -> wost_film_download"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "kernel": ("k_walk_persistent<%d>" if args.walk_mode.startswith("persistent") else "k_step_uniform<%d>") % dim, "bytes_per_walk_step": bps, "launches": int(kern_launches),
+                         "kernel": ("k_g_first+k_g_bounce+k_g_finish<%d>" if guided else ("k_walk_persistent<%d>" if args.walk_mode.startswith("persistent") else "k_step_uniform<%d>")) % dim, "bytes_per_walk_step": bps, "launches": int(kern_launches),
                          "avg_launch_ms": kern_ms / max(1, kern_launches), "kernel_share_of_step": kern_ms_max / dev_ms if dev_ms > 0 else None,
                          "peak_source": peak_src},
             "clocks": clocks,
         }
+        if guided:
+            line["guided"] = dict(it.train_stats, train_spp=gkw["train_spp_count"], network="DenseGrid 8x4 + MLP 32-64-64-64-48 (data/ladybug/n.json)")
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
