@@ -84,7 +84,8 @@ namespace wost
         GQueue in, out;
         const int *in_count; // items of this bounce (device)
         int *out_count;
-        int *cursor; // tile claim cursor
+        int *cursor; // tile / item claim cursor
+        unsigned long long *cursor64; // claim cursor of the first arrival (n_active * batch_samples may exceed 2^31)
         unsigned long long *steps;
         const uint32_t *active;
         int n_active;
@@ -173,47 +174,105 @@ namespace wost
         }
     }
 
-    // ---- depth 0: evaluation points (generateEvaluationPointsImpl + the stages of depth 0)
-    template <int D>
-    __global__ void __launch_bounds__(kGBlock) k_g_first(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
+    // ---- arrival of a walk at a new point: closest-point query + separate / boundary / source / Neumann stages.
+    // Persistent lanes with refill, like k_walk_persistent (integrator.cu): a lane owns one item at a time, the warp
+    // alternates between traversal trips (every lane with a query in flight opens one node) and a tail phase in which
+    // the lanes whose query has finished run the contribution stages, append the survivors to the out-shell queue
+    // (one atomic per warp) and claim new items (one atomic per warp). The number of node visits varies ~10x between
+    // neighbouring items; lock-step traversal (one item per lane per round) left 7 of 32 lanes busy
+    // (profiles/r1_notes.md), refilling keeps the traversal -- the bulk of the instructions -- near full width.
+    // First: items are synthesised from (pixel, sample) = generateEvaluationPointsImpl (integrator.cu:131-151).
+    constexpr int kGRefill = 6;
+    template <int D, bool First>
+    __global__ void __launch_bounds__(kGBlock) k_g_arrive(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
         uint2 spill_mem[kSpillLevels];
         st.init(smem_stack, a.overflow, spill_mem);
         const int lane = threadIdx.x & 31;
-        const long long n = (long long)a.n_active * a.batch_samples;
-        if (blockIdx.x == 0 && threadIdx.x == 0 && n > 0)
-            atomicAdd(a.steps, (unsigned long long)n);
+        const long long njobs = First ? (long long)a.n_active * a.batch_samples : (long long)*a.in_count;
+        GItem<D> it;
+        NearestTrav<D> t;
+        bool has = false, exhausted = false, trav = false;
+        unsigned int my_steps = 0;
+        it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
+        it.T[0] = it.T[1] = it.T[2] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            it.w.x[k] = it.w.nN[k] = 0.0f;
+        t.win = kInvalid, t.best = 0.0f;
         for (;;)
         {
-            long long base = 0;
-            if (lane == 0)
-                base = (long long)atomicAdd(a.cursor, 32);
-            base = __shfl_sync(kFullMask, base, 0);
-            if (base >= n)
-                break;
-            const long long i = base + lane;
-            const bool valid = i < n;
-            GItem<D> it;
-            it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 1.0f, it.w.onN = false;
-            it.R_B = 0.0f;
-            it.T[0] = it.T[1] = it.T[2] = 0.0f;
-#pragma unroll
-            for (int k = 0; k < D; ++k)
-                it.w.x[k] = it.w.nN[k] = 0.0f;
-            if (valid)
+            const unsigned trav_mask = __ballot_sync(kFullMask, trav);
+            const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has || !exhausted));
+            if (pend_mask != 0u && (__popc(pend_mask) >= kGRefill || trav_mask == 0u))
             {
-                const uint32_t sj = (uint32_t)(i / a.n_active);
-                it.w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
-                it.w.sample = a.sample0 + sj;
-                it.w.x = eval_point(c, it.w.pixel);
+                bool on = false;
+                if (!trav && has)
+                {
+                    PixelAccT<true> acc;
+                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
+                    acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
+                    on = walk_step_contrib<D>(c, it.w, a.depth, st, acc, nearest_distance(t), t.win, 1.0f, it.R_B);
+                    acc.flush();
+                    it.T[0] = acc.tot[0], it.T[1] = acc.tot[1], it.T[2] = acc.tot[2];
+                    if (!on)
+                        g_finalize<D>(a, it);
+                    has = false;
+                }
+                g_push<D>(a, it, on);
+                const bool want = !trav && !exhausted;
+                const unsigned want_mask = __ballot_sync(kFullMask, want);
+                if (want_mask != 0u)
+                {
+                    const int leader = __ffs(want_mask) - 1;
+                    long long base = 0;
+                    if (lane == leader)
+                        base = First ? (long long)atomicAdd(reinterpret_cast<unsigned long long *>(a.cursor64), (unsigned long long)__popc(want_mask))
+                                     : (long long)atomicAdd(a.cursor, __popc(want_mask));
+                    base = __shfl_sync(kFullMask, base, leader);
+                    if (want)
+                    {
+                        const long long i = base + __popc(want_mask & ((1u << lane) - 1u));
+                        if (i < njobs)
+                        {
+                            if (First)
+                            {
+                                const uint32_t sj = (uint32_t)(i / a.n_active);
+                                it.w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
+                                it.w.sample = a.sample0 + sj;
+                                it.w.x = eval_point(c, it.w.pixel);
+                                it.w.thp = 1.0f;
+                                it.w.onN = false;
+                                it.R_B = 0.0f;
+                                it.T[0] = it.T[1] = it.T[2] = 0.0f;
+#pragma unroll
+                                for (int k = 0; k < D; ++k)
+                                    it.w.nN[k] = 0.0f;
+                            }
+                            else
+                                g_load<D>(a.in, (size_t)i, it);
+                            has = true;
+                            ++my_steps;
+                            trav = nearest_begin<D, false>(c.dir, it.w.x, st, t);
+                        }
+                        else
+                            exhausted = true;
+                    }
+                }
             }
-            const bool alive = g_arrive<D>(c, it, 0u, st, a.acc, a.sample0, a.npix, valid);
-            if (valid && !alive)
-                g_finalize<D>(a, it);
-            g_push<D>(a, it, alive);
+            else if (trav_mask == 0u)
+                break;
+            if (trav)
+                trav = nearest_trip<D, false>(c.dir, it.w.x, st, t);
         }
+        unsigned int ws = my_steps;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+            ws += __shfl_xor_sync(kFullMask, ws, o);
+        if (lane == 0 && ws)
+            atomicAdd(a.steps, (unsigned long long)ws);
     }
 
     // Direction sampling of one out-shell item given the raw network output `raw` (kOut floats):
@@ -287,7 +346,6 @@ namespace wost
         if (fused)
             tmem_base = mlp_fwd_setup<K0>(sm, net.mlp);
         const int n = *a.in_count;
-        unsigned int my_steps = 0;
         for (;;)
         {
             __syncthreads();
@@ -327,7 +385,6 @@ namespace wost
                     raw[4 * k] = v.x, raw[4 * k + 1] = v.y, raw[4 * k + 2] = v.z, raw[4 * k + 3] = v.w;
                 }
             }
-            bool alive = false;
             if (valid)
             {
                 float pdf;
@@ -337,28 +394,20 @@ namespace wost
                 if ((int)a.depth + 1 < a.max_depth)
                 {
                     walk_advance<D>(c, it.w, dir, pdf, it.R_B, st);
-                    alive = true;
-                    ++my_steps;
+                    g_store<D>(a.out, (size_t)i, it); // same slot: k_g_arrive of depth + 1 reads the moved items 1:1
                 }
                 else
                     g_finalize<D>(a, it);
             }
-            const bool on = g_arrive<D>(c, it, a.depth + 1u, st, a.acc, a.sample0, a.npix, alive);
-            if (alive && !on)
-                g_finalize<D>(a, it);
-            g_push<D>(a, it, on);
         }
         if (fused)
             mlp_fwd_teardown<K0>(sm, tmem_base);
-        unsigned int ws = my_steps;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-            ws += __shfl_xor_sync(kFullMask, ws, o);
-        if ((threadIdx.x & 31) == 0 && ws)
-            atomicAdd(a.steps, (unsigned long long)ws);
     }
 
-    // ---- walks that outlive the guided depths: uniform steps to completion (oneStepWalkImpl, integrator.cu:882-965)
+    // ---- walks that outlive the guided depths: uniform steps to completion (oneStepWalkImpl, integrator.cu:882-965).
+    // Same persistent-lane scheme as k_g_arrive, but a lane keeps its walk until it ends: tail phase = contribution
+    // stages of the point just reached, then uniform direction + walk record + move; lanes without a walk claim the
+    // next out-shell item of the queue.
     template <int D>
     __global__ void __launch_bounds__(kGBlock) k_g_finish(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
     {
@@ -367,63 +416,86 @@ namespace wost
         uint2 spill_mem[kSpillLevels];
         st.init(smem_stack, a.overflow, spill_mem);
         const int lane = threadIdx.x & 31;
-        const int n = *a.in_count;
+        const int njobs = *a.in_count;
+        GItem<D> it;
+        NearestTrav<D> t;
+        uint32_t depth = a.depth;
+        bool has = false, exhausted = false, trav = false, need_contrib = false;
         unsigned int my_steps = 0;
+        it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
+        it.T[0] = it.T[1] = it.T[2] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            it.w.x[k] = it.w.nN[k] = 0.0f;
+        t.win = kInvalid, t.best = 0.0f;
         for (;;)
         {
-            int base = 0;
-            if (lane == 0)
-                base = atomicAdd(a.cursor, 32);
-            base = __shfl_sync(kFullMask, base, 0);
-            if (base >= n)
-                break;
-            const int i = base + lane;
-            bool alive = i < n;
-            GItem<D> it;
-            if (alive)
-                g_load<D>(a.in, (size_t)i, it);
-            else
+            const unsigned trav_mask = __ballot_sync(kFullMask, trav);
+            const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has || !exhausted));
+            if (pend_mask != 0u && (__popc(pend_mask) >= kGRefill || trav_mask == 0u))
             {
-                it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
-                it.T[0] = it.T[1] = it.T[2] = 0.0f;
-#pragma unroll
-                for (int k = 0; k < D; ++k)
-                    it.w.x[k] = it.w.nN[k] = 0.0f;
-            }
-            uint32_t depth = a.depth;
-            while (__any_sync(kFullMask, alive))
-            {
-                bool moved = false;
-                if (alive)
+                if (!trav && has && need_contrib)
+                {
+                    PixelAccT<true> acc;
+                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
+                    acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
+                    const bool on = walk_step_contrib<D>(c, it.w, depth, st, acc, nearest_distance(t), t.win, 1.0f, it.R_B);
+                    acc.flush();
+                    it.T[0] = acc.tot[0], it.T[1] = acc.tot[1], it.T[2] = acc.tot[2];
+                    need_contrib = false;
+                    if (!on)
+                    {
+                        g_finalize<D>(a, it);
+                        has = false;
+                    }
+                }
+                const bool want = !trav && !has && !exhausted;
+                const unsigned want_mask = __ballot_sync(kFullMask, want);
+                if (want_mask != 0u)
+                {
+                    const int leader = __ffs(want_mask) - 1;
+                    int base = 0;
+                    if (lane == leader)
+                        base = atomicAdd(a.cursor, __popc(want_mask));
+                    base = __shfl_sync(kFullMask, base, leader);
+                    if (want)
+                    {
+                        const int i = base + __popc(want_mask & ((1u << lane) - 1u));
+                        if (i < njobs)
+                        {
+                            g_load<D>(a.in, (size_t)i, it);
+                            depth = a.depth;
+                            has = true;
+                        }
+                        else
+                            exhausted = true;
+                    }
+                }
+                if (!trav && has)
                 {
                     float pdf;
                     const Vec<D> dir = uniform_direction<D>(c, it.w, depth, pdf);
                     if (a.training && depth < (uint32_t)a.max_train_depth)
-                    {
-                        GArgs b = a;
-                        b.depth = depth;
-                        g_record<D>(b, it, dir, pdf, depth);
-                    }
+                        g_record<D>(a, it, dir, pdf, depth);
                     if ((int)depth + 1 < a.max_depth)
                     {
                         walk_advance<D>(c, it.w, dir, pdf, it.R_B, st);
-                        moved = true;
+                        ++depth;
                         ++my_steps;
+                        need_contrib = true;
+                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t);
                     }
                     else
                     {
                         g_finalize<D>(a, it);
-                        alive = false;
+                        has = false;
                     }
                 }
-                const bool on = g_arrive<D>(c, it, depth + 1u, st, a.acc, a.sample0, a.npix, moved);
-                if (moved && !on)
-                {
-                    g_finalize<D>(a, it);
-                    alive = false;
-                }
-                ++depth;
             }
+            else if (trav_mask == 0u)
+                break;
+            if (trav)
+                trav = nearest_trip<D, false>(c.dir, it.w.x, st, t);
         }
         unsigned int ws = my_steps;
 #pragma unroll
@@ -1139,7 +1211,7 @@ namespace wost
         int occ = 1;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_bounce<D, K0>, kGBlock, smem) != cudaSuccess)
             occ = 1;
-        return sm_count() * std::max(1, std::min(occ, 512 / kTmemColsFwd));
+        return sm_count() * std::max(2, std::min(occ, 512 / kTmemColsFwd)); // >= 2: CTAs beyond residency just find the cursor exhausted
     }
     template <int D, int K0>
     static wost_status launch_train(wost_integrator *it, const TrainArgs &ta)
@@ -1241,7 +1313,7 @@ namespace wost
         const int S = it->spp_batch;
         const size_t stack_smem = stack_smem_bytes(kGBlock);
         int occ = 1;
-        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_first<D>, kGBlock, stack_smem));
+        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_arrive<D, false>, kGBlock, stack_smem));
         const int grid_full = sm_count() * std::max(1, occ);
         int grid_bounce = sm_count();
         WOST_DISPATCH_K0(D, n.k0, (grid_bounce = bounce_grid<D, K0_>()));
@@ -1273,7 +1345,8 @@ namespace wost
             const int maxGuided = training ? it->s.max_guided_depth_training : it->s.max_guided_depth_guiding;
             const float ufrac = training ? it->s.uniform_fraction_training : it->s.uniform_fraction_guiding;
             const int G = std::max(0, std::min(maxGuided, maxd));
-            WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int) * (size_t)(2 * (maxd + 2)), st));
+            WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int) * (size_t)(3 * (maxd + 2)), st));
+            WOST_CUDA_TRY(cudaMemsetAsync(it->d_cursor64.ptr, 0, sizeof(unsigned long long), st));
             if (training)
                 WOST_CUDA_TRY(cudaMemsetAsync(g.rec_count.ptr, 0, sizeof(int) * (size_t)it->npix, st));
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi], st));
@@ -1289,20 +1362,21 @@ namespace wost
             a.rec = g.rec.ptr, a.rec_onN = g.rec_onN.ptr, a.rec_count = g.rec_count.ptr, a.total = g.total.ptr;
             auto queue = [&](int i)
             { return GQueue{it->gq[i][0].ptr, it->gq[i][1].ptr, it->gq[i][2].ptr, it->gq3[i].ptr}; };
-            int *counts = it->d_counts.ptr, *cursors = it->d_counts.ptr + (maxd + 2);
-            // depth 0
+            int *counts = it->d_counts.ptr, *cur_b = counts + (maxd + 2), *cur_a = counts + 2 * (maxd + 2);
+            // depth 0: evaluation points -> out-shell items of depth 0 in queue 0
             a.in = queue(1), a.out = queue(0);
-            a.in_count = nullptr, a.out_count = counts + 0, a.cursor = cursors + 0, a.depth = 0;
+            a.in_count = nullptr, a.out_count = counts + 0, a.cursor = cur_a + 0, a.cursor64 = it->d_cursor64.ptr, a.depth = 0;
             {
                 const long long n0 = (long long)it->n_active * Sb;
                 const int grid = (int)std::min<long long>(grid_full, (n0 + kGBlock - 1) / kGBlock);
-                k_g_first<D><<<std::max(1, grid), kGBlock, stack_smem, st>>>(ctx, a);
+                k_g_arrive<D, true><<<std::max(1, grid), kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }
+            // out-shell items of depth d live in queue d & 1
             for (int d = 0; d < G; ++d)
             {
-                a.in = queue(d & 1), a.out = queue((d + 1) & 1);
-                a.in_count = counts + d, a.out_count = counts + d + 1, a.cursor = cursors + d + 1, a.depth = (uint32_t)d;
+                a.in = queue(d & 1), a.out = queue(d & 1); // the bounce moves its items in place
+                a.in_count = counts + d, a.out_count = nullptr, a.cursor = cur_b + d, a.depth = (uint32_t)d;
                 a.precomputed = nullptr;
                 if (it->s.mlp_impl == 1)
                 {
@@ -1312,11 +1386,18 @@ namespace wost
                 }
                 WOST_DISPATCH_K0(D, n.k0, (launch_bounce<D, K0_>(it, ctx, a, grid_bounce)));
                 ++it->launches, ++it->step_launches;
+                if (d + 1 < maxd)
+                {
+                    a.in = queue(d & 1), a.out = queue((d + 1) & 1);
+                    a.in_count = counts + d, a.out_count = counts + d + 1, a.cursor = cur_a + d + 1, a.depth = (uint32_t)(d + 1);
+                    k_g_arrive<D, false><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
+                    ++it->launches, ++it->step_launches;
+                }
             }
             if (G < maxd)
             {
                 a.in = queue(G & 1), a.out = queue((G + 1) & 1);
-                a.in_count = counts + G, a.out_count = counts + G + 1, a.cursor = cursors + G + 1, a.depth = (uint32_t)G;
+                a.in_count = counts + G, a.out_count = nullptr, a.cursor = cur_b + G, a.depth = (uint32_t)G;
                 k_g_finish<D><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }

@@ -675,9 +675,9 @@ extern "C"
             if (it->dim == 3 && it->qc[i].alloc(it->queue_capacity) != cudaSuccess)
                 return fail("queue allocation");
         }
-        if (kind == WOST_GUIDED && guided_alloc(it) != WOST_OK)
+        if (kind == WOST_GUIDED && (it->d_cursor64.alloc(1) != cudaSuccess || guided_alloc(it) != WOST_OK))
             return fail("guided buffer allocation");
-        if (it->d_counts.alloc((size_t)2 * (s.max_walking_depth + 2)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
+        if (it->d_counts.alloc((size_t)3 * (s.max_walking_depth + 2)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
             it->d_acc.alloc((size_t)S * it->npix) != cudaSuccess || it->d_overflow.alloc(1) != cudaSuccess)
             return fail("buffer allocation");
         for (int c = 0; c < WOST_CH_COUNT; ++c)

@@ -47,6 +47,7 @@ struct wost_integrator
     wost::GuidedBuffers gb;
     wost::DevBuf<float4> gq[2][3]; // guided out-shell queues: {x,thp} {n,R_B} {pixel,sample|onN,Tr,Tg}
     wost::DevBuf<float> gq3[2];    // Tb
+    wost::DevBuf<unsigned long long> d_cursor64;
     wost_allreduce_fn allreduce = nullptr;
     void *allreduce_user = nullptr;
     uint64_t train_samples = 0, train_steps = 0;
