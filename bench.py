@@ -377,6 +377,8 @@ def main():
             "clocks": clocks,
         }
         if guided:
+            if os.environ.get("WOST_PROFILE"):
+                line["profile_ms_last_solve"] = it.profile
             line["guided"] = dict(it.train_stats, train_spp=gkw["train_spp_count"], network="DenseGrid 8x4 + MLP 32-64-64-64-48 (data/ladybug/n.json)")
         if cpu is not None:
             line["cpu_baseline"] = cpu

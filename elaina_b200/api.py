@@ -404,6 +404,13 @@ class GuidedIntegrator(_Integrator):
         check(_lib.load().wost_set_allreduce(self.h, ctypes.cast(self._cb, c_void_p), None))
 
     @property
+    def profile(self):
+        """device ms of the last solve by kernel class (needs WOST_PROFILE=1 in the environment)"""
+        out = np.zeros(8, np.float32)
+        check(_lib.load().wost_guided_last_profile(self.h, _p(out)))
+        return dict(arrive=float(out[0]), bounce=float(out[1]), finish=float(out[2]), gaps=float(out[3]), train=float(out[4]))
+
+    @property
     def train_stats(self):
         a, b, l = c_u64(), c_u64(), c_float()
         check(_lib.load().wost_guided_last_stats(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(l)))

@@ -23,6 +23,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "json.h"
@@ -888,11 +889,15 @@ namespace wost
                         break;
                     GridCell<D> cell;
                     grid_cell<D>(net, l, xn, cell);
+                    // one 128-bit reduction per corner (red.global.add.v4.f32, sm_90+): the 4 features of a grid point are
+                    // contiguous and 16-byte aligned -- 4x fewer atomics than tcnn's per-feature-pair adds (grid.h:437-446)
 #pragma unroll
                     for (int corner = 0; corner < (1 << D); ++corner)
-#pragma unroll
-                        for (int f = 0; f < kGridFeat; ++f)
-                            atomicAdd(gg + (size_t)cell.idx[corner] * kGridFeat + f, cell.w[corner] * de[l * kGridFeat + f]);
+                    {
+                        const float w = cell.w[corner];
+                        atomicAdd(reinterpret_cast<float4 *>(gg + (size_t)cell.idx[corner] * kGridFeat),
+                                  make_float4(w * de[l * kGridFeat], w * de[l * kGridFeat + 1], w * de[l * kGridFeat + 2], w * de[l * kGridFeat + 3]));
+                    }
                 }
             }
             // ---- weight gradients, accumulated in TMEM over all tiles of this CTA:
@@ -1323,6 +1328,23 @@ namespace wost
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0, it->step_launches = 0, it->step_kernel_ms = 0.0f;
         it->train_samples = 0, it->train_steps = 0;
+        // optional per-kernel-class device timing (WOST_PROFILE=1): CUDA events around every launch of the solve
+        const bool prof = getenv("WOST_PROFILE") != nullptr;
+        size_t prof_used = 0;
+        std::vector<int> prof_cls;
+        auto prof_mark = [&](int cls)
+        {
+            if (!prof)
+                return;
+            if (prof_used == it->prof_ev.size())
+            {
+                cudaEvent_t e;
+                cudaEventCreate(&e);
+                it->prof_ev.push_back(e);
+            }
+            cudaEventRecord(it->prof_ev[prof_used++], st);
+            prof_cls.push_back(cls);
+        };
         std::vector<std::pair<int, int>> batches; // (first sample, count)
         for (int s0 = 0; s0 < spp;)
         {
@@ -1369,6 +1391,7 @@ namespace wost
             {
                 const long long n0 = (long long)it->n_active * Sb;
                 const int grid = (int)std::min<long long>(grid_full, (n0 + kGBlock - 1) / kGBlock);
+                prof_mark(0);
                 k_g_arrive<D, true><<<std::max(1, grid), kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }
@@ -1384,12 +1407,14 @@ namespace wost
                     a.precomputed = g.infer_out.ptr;
                     ++it->launches;
                 }
+                prof_mark(1);
                 WOST_DISPATCH_K0(D, n.k0, (launch_bounce<D, K0_>(it, ctx, a, grid_bounce)));
                 ++it->launches, ++it->step_launches;
                 if (d + 1 < maxd)
                 {
                     a.in = queue(d & 1), a.out = queue((d + 1) & 1);
                     a.in_count = counts + d, a.out_count = counts + d + 1, a.cursor = cur_a + d + 1, a.depth = (uint32_t)(d + 1);
+                    prof_mark(0);
                     k_g_arrive<D, false><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
                     ++it->launches, ++it->step_launches;
                 }
@@ -1398,17 +1423,21 @@ namespace wost
             {
                 a.in = queue(G & 1), a.out = queue((G + 1) & 1);
                 a.in_count = counts + G, a.out_count = nullptr, a.cursor = cur_b + G, a.depth = (uint32_t)G;
+                prof_mark(2);
                 k_g_finish<D><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }
+            prof_mark(3);
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));
             WOST_CUDA_TRY(cudaGetLastError());
             if (training)
             {
+                prof_mark(4);
                 const wost_status rc = train_frame<D>(it, ctx);
                 if (rc != WOST_OK)
                     return rc;
             }
+            prof_mark(3);
             // the accumulator slots are summed into slot 0 between batches of different sizes? No: slot s of every batch
             // adds to acc[s]; k_resolve sums all S slots at the end, so a training batch (1 sample) simply uses slot 0.
         }
@@ -1431,6 +1460,14 @@ namespace wost
             float f = 0.0f;
             WOST_CUDA_TRY(cudaEventElapsedTime(&f, it->batch_ev[2 * bi], it->batch_ev[2 * bi + 1]));
             it->step_kernel_ms += f;
+        }
+        for (int k = 0; k < 8; ++k)
+            it->prof_ms[k] = 0.0f;
+        for (size_t k = 0; k + 1 < prof_used; ++k)
+        {
+            float f = 0.0f;
+            cudaEventElapsedTime(&f, it->prof_ev[k], it->prof_ev[k + 1]);
+            it->prof_ms[prof_cls[k]] += f; // the time from a mark to the next one belongs to that mark's class
         }
         it->train_steps = (uint64_t)h_ctl.opt_steps[0];
         it->train_samples = (uint64_t)h_ctl.n_samples;
@@ -1713,6 +1750,14 @@ extern "C"
             return WOST_ERR_INVALID;
         it->allreduce = fn;
         it->allreduce_user = user;
+        return WOST_OK;
+    }
+    wost_status wost_guided_last_profile(wost_integrator *it, float *ms8)
+    {
+        if (!it || !ms8)
+            return WOST_ERR_INVALID;
+        for (int k = 0; k < 8; ++k)
+            ms8[k] = it->prof_ms[k];
         return WOST_OK;
     }
     wost_status wost_guided_last_stats(wost_integrator *it, uint64_t *train_samples, uint64_t *train_steps, float *last_loss)

@@ -52,10 +52,14 @@ struct wost_integrator
     void *allreduce_user = nullptr;
     uint64_t train_samples = 0, train_steps = 0;
     float last_loss = 0.0f;
+    std::vector<cudaEvent_t> prof_ev; // WOST_PROFILE=1
+    float prof_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
     ~wost_integrator()
     {
         for (cudaEvent_t e : batch_ev)
+            cudaEventDestroy(e);
+        for (cudaEvent_t e : prof_ev)
             cudaEventDestroy(e);
         if (ev0)
             cudaEventDestroy(ev0);

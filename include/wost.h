@@ -199,6 +199,10 @@ extern "C"
      * callback must enqueue a SUM all-reduce on `stream` (a cudaStream_t) and return 0. */
     typedef int (*wost_allreduce_fn)(void *user, void *d_buf, uint64_t n_floats, void *stream);
     wost_status wost_set_allreduce(wost_integrator *it, wost_allreduce_fn fn, void *user);
+    /* with WOST_PROFILE=1 in the environment: device ms of the last guided solve by kernel class
+     * [0] arrive (closest point + contributions), [1] bounce (MLP + sampling + move), [2] finish (uniform tail),
+     * [3] gaps between classes, [4] training frames (samples + forward/backward + optimiser), [5..7] unused */
+    wost_status wost_guided_last_profile(wost_integrator *it, float *ms8);
     /* counters of the last guided solve: training samples consumed, optimiser steps, mean loss of the last batch */
     wost_status wost_guided_last_stats(wost_integrator *it, uint64_t *train_samples, uint64_t *train_steps, float *last_loss);
 

@@ -288,3 +288,36 @@ def test_guided_training_samples_match_oracle(oracle):
     np.testing.assert_allclose(it.get_params(), params, atol=1e-7)  # lr = 0: weights untouched
     sol_g = it.film()[..., :3].reshape(-1, 3)
     assert np.isclose(sol_g, sol_o, rtol=2e-3, atol=2e-3).mean() > 0.9
+
+
+def test_guided_3d_vmf_vs_oracle_and_training(oracle):
+    """3D: vMF lobes, Poisson source term, triangles. Fixed weights vs the oracle's guided walker, then a short
+    training run (records -> samples -> tcgen05 training kernel with K0 = 16, D = 3) that must stay finite."""
+    from elaina_b200 import api, scenes
+    dv, dp = scenes.icosphere(3, 1.0, 0.05)
+    src = np.ones((8, 8, 8, 3), np.float32) * 0.5
+    spec = dict(dim=3, dverts=dv, dprims=dp, color_dirichlet=scenes.gray_pairs(scenes.harmonic_3d(dv)),
+                source=src, source_origin=(-1.6, -1.6, -1.6), source_voxel=0.4, source_intensity=1.0,
+                grid_scale=0.7, grid_pos=(0.0, 0.0, 0.1), grid_up=(0.0, 1.0, 0.0), grid_right=(1.0, 0.0, 0.0),
+                aabb_min=(-1.2, -1.2, -1.2), aabb_max=(1.2, 1.2, 1.2))
+    oprob, gprob = build_both(oracle, spec)
+    W, spp, depth = 20, 6, 24
+    it = _guided(gprob, frame=(W, W), depth=depth, spp=spp, eps=4e-3, seed=17, train_spp_count=0, max_guided_depth_guiding=5,
+                 uniform_fraction_guiding=0.5, spp_batch=2)
+    rng = np.random.RandomState(6)
+    params = (rng.randn(it.n_params) * 0.2).astype(np.float32)
+    it.set_params(params)
+    it.solve()
+    sol_g = it.film()[..., :3].reshape(-1, 3)
+    net = _oracle_net(oracle, it, NET_SMALL, spec["aabb_min"], spec["aabb_max"], params)
+    st = dict(frame_w=W, frame_h=W, max_walking_depth=depth, samples_per_pixel=spp, epsilon_shell=4e-3, seed=17)
+    sol_o, steps_o, _ = oracle.solve_guided(oprob, st, net, max_guided_depth=5, uniform_fraction=0.5)
+    assert abs(it.last_walk_steps - steps_o) <= 0.02 * steps_o
+    assert np.isclose(sol_g, sol_o, rtol=5e-3, atol=5e-3).mean() > 0.85
+    assert np.all(_stderr_band(sol_g, sol_o, sigma=2.0, spp=spp))
+    it2 = _guided(gprob, frame=(32, 32), depth=depth, spp=12, eps=4e-3, seed=3, train_spp_count=8, max_guided_depth_training=5,
+                  max_guided_depth_guiding=5, uniform_fraction_training=0.5, uniform_fraction_guiding=0.5, train_min_batch=512, train_batch_size=2048)
+    it2.solve()
+    stats = it2.train_stats
+    assert stats["steps"] >= 8 and np.isfinite(stats["loss"])
+    assert np.isfinite(it2.get_params()).all() and np.isfinite(it2.film()).all()
