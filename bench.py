@@ -213,6 +213,7 @@ def main():
     import torch
     import torch.distributed as dist
     from elaina_b200 import api
+    from elaina_b200 import dist as wdist
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA GPU (there is no CPU fallback for the walker)")
     torch.cuda.set_device(local_rank)
@@ -244,7 +245,7 @@ def main():
     W, H = wl["frame"]
     # strong scaling: the frame is fixed, rows are dealt to ranks in interleaved tiles of 4 rows (pixel-keyed RNG ->
     # the summed film does not depend on N)
-    shard = dict(pixel_stride_rows=4, num_shards=world, shard=rank) if world > 1 else {}
+    shard = wdist.shard_kwargs(rank, world, stride_rows=4)
     guided = args.integrator == "guided"
     gkw = {}
     if guided:
@@ -261,6 +262,8 @@ def main():
 
     prob = make_problem()
     it = Integrator(prob, settings)
+    if guided and world > 1:
+        wdist.install_gradient_allreduce(it, dev)  # NCCL sum of the gradient slab on the integrator's stream, per batch
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     film_t = None
@@ -304,11 +307,13 @@ def main():
     def e2e_once():
         p = make_problem()
         i2 = Integrator(p, settings)
+        if guided and world > 1:
+            wdist.install_gradient_allreduce(i2, dev)
         i2.solve()
         if world > 1:
             # final film gather: shards own disjoint rows and write zeros elsewhere -> one NCCL sum
             ptr = i2.film_device_ptr()
-            film = _wrap_device_ptr(torch, ptr, H * W * 5, dev)
+            film = wdist.wrap_device_ptr(ptr, H * W * 5, dev)
             film_t.copy_(film)
             dist.all_reduce(film_t)
             out = film_t.cpu() if rank == 0 else None
@@ -385,15 +390,6 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
-
-
-def _wrap_device_ptr(torch, ptr, n_floats, dev):
-    """A float32 torch view over a device pointer owned by libwost.so (for NCCL collectives issued from Python)."""
-    class _Holder:
-        pass
-    h = _Holder()
-    h.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
-    return torch.as_tensor(h, device=dev)
 
 
 if __name__ == "__main__":

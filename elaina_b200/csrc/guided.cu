@@ -1270,7 +1270,8 @@ namespace wost
         k_g_scatter_samples<D><<<div_up(it->n_active, 256), 256, 0, st>>>(ctx, it->d_active.ptr, it->n_active, it->npix, g.rec.ptr, g.rec_onN.ptr,
                                                                              g.rec_count.ptr, g.total.ptr, g.sample_off.ptr, g.cap, g.smp.ptr, g.smp_onN.ptr, n.ctl.ptr);
         it->launches += 4;
-        const int max_batches = std::min(per_frame, g.cap / bs + 1);
+        // with a gradient all-reduce every rank must issue the same number of collectives, whatever its own sample count
+        const int max_batches = it->allreduce ? per_frame : std::min(per_frame, g.cap / bs + 1);
         for (int iter = 0; iter < max_batches; ++iter)
         {
             WOST_CUDA_TRY(cudaMemsetAsync(n.grad.ptr, 0, sizeof(float) * ((size_t)n.n_params + 4), st));
