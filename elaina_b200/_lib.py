@@ -104,6 +104,7 @@ SYMBOLS = [
     ("wost_film_device_ptr", c_int, [c_void_p, c_int, _PP(c_void_p)]),
     ("wost_last_launch_count", c_int, [c_void_p, _PP(c_u64)]),
     ("wost_last_step_kernel_time", c_int, [c_void_p, _PP(c_u64), _PP(c_float)]),
+    ("wost_run_config", c_int, [c_char_p]),
     ("wost_reset_network", c_int, [c_void_p, c_char_p]),
     ("wost_reset_training", c_int, [c_void_p]),
     ("wost_query_network", c_int, [c_void_p, c_void_p, c_void_p]),

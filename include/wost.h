@@ -169,6 +169,11 @@ extern "C"
      * integrator's stream around each spp batch's run of step launches) -- the roofline numerator of bench.py */
     wost_status wost_last_step_kernel_time(wost_integrator *it, uint64_t *step_launches, float *step_kernel_ms);
 
+    /* ------------------------------------------------------------------ configuration runner
+     * run_expr(conf_path) (exec.cu:39-221): parse an elaina-exec configuration file, build problem and integrator, run
+     * the requested channels, export images, write <base_path>/<exp_name>/{conf.json,result.json,...}. */
+    wost_status wost_run_config(const char *json_path);
+
     /* ------------------------------------------------------------------ guided integrator: the guiding network
      * resetNetwork(json) (integrator/guided/integrator.cu:1096-1137): `tcnn_json` is the "network" block of the
      * configuration file ({encoding{otype DenseGrid,n_levels,n_features_per_level 4,base_resolution,per_level_scale},
