@@ -189,6 +189,7 @@ namespace wost
         uint32_t depth = 0;
         bool has_walk = false, exhausted = false, trav = false;
         unsigned int my_steps = 0;
+        float bound = dm_inf(); // upper bound of the next closest-point distance: R_D of this step + the distance moved
         w.pixel = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
 #pragma unroll
         for (int k = 0; k < D; ++k)
@@ -204,11 +205,14 @@ namespace wost
                 {
                     PixelAcc acc;
                     acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
-                    const bool alive = walk_step_tail<D>(c, w, depth, st, acc, nearest_distance(t), t.win);
+                    const Vec<D> x0 = w.x;
+                    const float R_D = nearest_distance(t);
+                    const bool alive = walk_step_tail<D>(c, w, depth, st, acc, R_D, t.win);
                     acc.flush();
                     ++depth;
                     if (!alive || depth >= (uint32_t)a.max_depth)
                         has_walk = false;
+                    bound = (R_D + vlen(vsub(w.x, x0))) * 1.00001f; // triangle inequality, rounding slack on top
                 }
                 const bool want = !has_walk && !exhausted;
                 const unsigned want_mask = __ballot_sync(kFullMask, want);
@@ -235,6 +239,7 @@ namespace wost
                                 w.nN[k] = 0.0f;
                             depth = 0;
                             has_walk = true;
+                            bound = dm_inf();
                         }
                         else
                             exhausted = true;
@@ -243,7 +248,7 @@ namespace wost
                 if (!trav && has_walk)
                 {
                     ++my_steps;
-                    trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t);
+                    trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t, bound);
                 }
             }
             else if (trav_mask == 0u)

@@ -351,8 +351,11 @@ namespace wost
         st.sp = 0;
     }
     // -> true when trips are needed; false when the result is already in t (0 or 1 primitives)
+    // bound: an a-priori upper bound of the result (inf when unknown). A walk that moved by s from a point whose
+    // closest distance was R knows d(x') <= R + s; seeding the pruning threshold with it keeps the far siblings of the
+    // first descent off the stack (they are otherwise pushed, and popped later only to be discarded).
     template <int D, bool RefOrder>
-    WOST_DEV bool nearest_begin(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
+    WOST_DEV bool nearest_begin(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t, float bound = dm_inf())
     {
         t.win = kInvalid;
         t.best = dm_inf();
@@ -381,7 +384,10 @@ namespace wost
             return true;
         }
         t.slack = fmax_nn(qmax, bvh.max_abs_coord) * 1.9073486328125e-06f; // 2^-19
-        t.thr = dm_inf();
+        {
+            const float u = bound + t.slack; // inf stays inf
+            t.thr = u * u;
+        }
         t.best_rank = 0;
         t.have_rank = false;
         t.n_near = 0;
