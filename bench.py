@@ -36,7 +36,7 @@ METRIC = "walk_steps_per_sec"
 UNIT = "walk-steps/s"
 
 # algorithmic bytes per walk-step (DESIGN.md "Roofline"): state in/out + one root->leaf descent per query
-BYTES_PER_STEP = {"c3": 938, "c3-small": 938, "c4": 1910, "c1": 1850}
+BYTES_PER_STEP = {"c3": 938, "c3-small": 938, "c4": 1734, "c4-small": 1734, "c1": 1850}  # c4: 1910 with guiding I/O (added below)
 
 
 def workload(name):
@@ -58,17 +58,32 @@ def workload(name):
                     grid_scale=1.5, grid_pos=(0.0, 0.0), grid_up=(0.0, 1.0), aabb_min=(-1.5, -1.5), aabb_max=(1.5, 1.5),
                     frame=(W, W), depth=64, spp=spp, eps=1e-3 * diag, seed=42,
                     desc="synthetic 2D Laplace, %d-segment star polygon, g=Re(z^3), %dx%d grid masked to the interior (%d active pixels), %d spp, depth 64" % (nseg, W, W, int(mask.sum()), spp))
-    if name == "c4":
-        # configs[3] shape at single-GPU bench scale: 3D Poisson on a displaced icosphere (uniform integrator)
-        dv, dp = scenes.icosphere(7, 1.0, 0.1)  # 327,680 triangles
+    if name == "c1":
+        # configs[0] shape (data/ladybug: 61 476 open strokes + 4-segment Neumann square, AABB [-100,600]^2, grid [0,500]^2,
+        # epsilonShell 1, depth 64); the shipped OBJ does not travel to the GPU box and its color.json is missing, so the
+        # scene is a seeded stroke soup of the same size (60 strokes x 1024 segments = 61 440 segments)
+        dv, dp = scenes.stroke_soup(60, 1024)
+        nv = np.array([[0, 0], [500, 0], [500, 500], [0, 500]], np.float32)
+        npr = np.array([[0, 1], [1, 2], [2, 3], [3, 0]], np.int32)
+        return dict(dim=2, dverts=dv, dprims=dp, nverts=nv, nprims=npr, color_dirichlet=scenes.stroke_colors(60, 1024), color_neumann=None,
+                    grid_scale=250.0, grid_pos=(250.0, 250.0), grid_up=(-1.0, 0.0), aabb_min=(-100.0, -100.0), aabb_max=(600.0, 600.0),
+                    frame=(1024, 1024), depth=64, spp=256, eps=1.0, seed=42,
+                    desc="synthetic ladybug-shaped 2D mixed problem: 61440-segment Dirichlet stroke soup in a 4-segment Neumann square, 1024x1024 grid, 256 spp, depth 64, epsilonShell 1")
+    if name in ("c4", "c4-small"):
+        # configs[3]: synthetic 3D Poisson on a displaced icosphere (1,310,720 triangles; c4-small 327,680), one 512x512 slice
+        dv, dp = scenes.icosphere(8 if name == "c4" else 7, 1.0, 0.1)
         src = np.ones((16, 16, 16, 3), np.float32)
-        return dict(dim=3, dverts=dv, dprims=dp, nverts=None, nprims=None,
+        # interior problem (like c3): evaluate the pixels of the slice that lie inside the surface (r >= 0.9 everywhere)
+        g = 2.0 * np.arange(512, dtype=np.float64) / 512 - 1.0
+        X, Y = np.meshgrid(g, g)
+        mask = (np.hypot(X, Y) < 0.88).astype(np.uint8)
+        return dict(dim=3, dverts=dv, dprims=dp, nverts=None, nprims=None, mask=mask,
                     color_dirichlet=scenes.gray_pairs(scenes.harmonic_3d(dv)), color_neumann=None,
                     source=src, source_origin=(-1.6, -1.6, -1.6), source_voxel=0.2,
                     grid_scale=1.0, grid_pos=(0.0, 0.0, 0.0), grid_up=(0.0, 1.0, 0.0), grid_right=(1.0, 0.0, 0.0),
                     aabb_min=(-1.5, -1.5, -1.5), aabb_max=(1.5, 1.5, 1.5),
                     frame=(512, 512), depth=64, spp=64, eps=2e-3, seed=42,
-                    desc="synthetic 3D Poisson, 327,680-triangle displaced icosphere, 512x512 slice, 64 spp, depth 64")
+                    desc="synthetic 3D Poisson, %d-triangle displaced icosphere, 512x512 slice z=0 masked to the interior (%d active pixels), 64 spp, depth 64" % (len(dp), int(mask.sum())))
     raise SystemExit("unknown workload " + name)
 
 

@@ -89,6 +89,7 @@ namespace wost
         unsigned long long *cursor64; // claim cursor of the first arrival (n_active * batch_samples may exceed 2^31)
         unsigned long long *steps;
         const uint32_t *active;
+        const uint2 *first; // first-step cache (k_first_hit), indexed like `active`
         int n_active;
         uint32_t sample0;
         int batch_samples;
@@ -241,7 +242,8 @@ namespace wost
                             if (First)
                             {
                                 const uint32_t sj = (uint32_t)(i / a.n_active);
-                                it.w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
+                                const long long ai = i - (long long)sj * a.n_active;
+                                it.w.pixel = __ldg(a.active + ai);
                                 it.w.sample = a.sample0 + sj;
                                 it.w.x = eval_point(c, it.w.pixel);
                                 it.w.thp = 1.0f;
@@ -251,12 +253,22 @@ namespace wost
 #pragma unroll
                                 for (int k = 0; k < D; ++k)
                                     it.w.nN[k] = 0.0f;
+                                // the closest-point query of an evaluation point is answered once per solve (k_first_hit)
+                                const uint2 f = __ldg(a.first + ai);
+                                t.win = f.x;
+                                t.best = __uint_as_float(f.y);
                             }
                             else
                                 g_load<D>(a.in, (size_t)i, it);
                             has = true;
                             ++my_steps;
-                            trav = nearest_begin<D, false>(c.dir, it.w.x, st, t);
+                            if (!First)
+                            {
+                                // the bounce moved the walk by R_B * dir from a point whose closest distance was R_D; without a
+                                // Neumann mesh R_B = max(1e-4, R_D) >= R_D, so d(x') <= 2 R_B (triangle inequality + rounding slack)
+                                const float bound = c.neu.nprims == 0 ? it.R_B * 2.0002f : dm_inf();
+                                trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, bound);
+                            }
                         }
                         else
                             exhausted = true;
@@ -422,6 +434,7 @@ namespace wost
         NearestTrav<D> t;
         uint32_t depth = a.depth;
         bool has = false, exhausted = false, trav = false, need_contrib = false;
+        float rd = dm_inf(); // closest distance at the point the walk is about to leave (upper-bounds the next query)
         unsigned int my_steps = 0;
         it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
         it.T[0] = it.T[1] = it.T[2] = 0.0f;
@@ -440,7 +453,8 @@ namespace wost
                     PixelAccT<true> acc;
                     acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
                     acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
-                    const bool on = walk_step_contrib<D>(c, it.w, depth, st, acc, nearest_distance(t), t.win, 1.0f, it.R_B);
+                    rd = nearest_distance(t);
+                    const bool on = walk_step_contrib<D>(c, it.w, depth, st, acc, rd, t.win, 1.0f, it.R_B);
                     acc.flush();
                     it.T[0] = acc.tot[0], it.T[1] = acc.tot[1], it.T[2] = acc.tot[2];
                     need_contrib = false;
@@ -467,6 +481,7 @@ namespace wost
                             g_load<D>(a.in, (size_t)i, it);
                             depth = a.depth;
                             has = true;
+                            rd = c.neu.nprims == 0 ? it.R_B : dm_inf(); // R_B = max(1e-4, R_D) when there is no Neumann mesh
                         }
                         else
                             exhausted = true;
@@ -480,11 +495,12 @@ namespace wost
                         g_record<D>(a, it, dir, pdf, depth);
                     if ((int)depth + 1 < a.max_depth)
                     {
+                        const Vec<D> x0 = it.w.x;
                         walk_advance<D>(c, it.w, dir, pdf, it.R_B, st);
                         ++depth;
                         ++my_steps;
                         need_contrib = true;
-                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t);
+                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, (rd + vlen(vsub(it.w.x, x0))) * 1.00001f);
                     }
                     else
                     {
@@ -1360,6 +1376,17 @@ namespace wost
             WOST_CUDA_TRY(cudaEventCreate(&e));
             it->batch_ev.push_back(e);
         }
+        if (it->n_active > 0 && !batches.empty())
+        {
+            if (it->d_first.count < (size_t)it->n_active && it->d_first.alloc((size_t)it->n_active) != cudaSuccess)
+            {
+                set_last_error("wost_solve: first-hit cache allocation failed");
+                return WOST_ERR_CUDA;
+            }
+            const int grid = std::max(1, std::min(grid_full, div_up(it->n_active, kGBlock)));
+            k_first_hit<D, false><<<grid, kGBlock, stack_smem, st>>>(ctx, it->d_active.ptr, it->n_active, it->d_first.ptr, it->d_overflow.ptr);
+            ++it->launches;
+        }
         for (size_t bi = 0; it->n_active > 0 && bi < batches.size(); ++bi)
         {
             const int s0 = batches[bi].first, Sb = batches[bi].second;
@@ -1377,6 +1404,7 @@ namespace wost
             memset(&a, 0, sizeof(a));
             a.steps = it->d_steps.ptr;
             a.active = it->d_active.ptr, a.n_active = it->n_active;
+            a.first = it->d_first.ptr;
             a.sample0 = (uint32_t)s0, a.batch_samples = Sb;
             a.acc = it->d_acc.ptr, a.npix = it->npix, a.max_depth = maxd, a.overflow = it->d_overflow.ptr;
             a.training = training ? 1 : 0;

@@ -163,6 +163,7 @@ namespace wost
     struct PersistArgs
     {
         const uint32_t *active;
+        const uint2 *first; // first-step cache (k_first_hit), indexed like `active`
         int n_active;
         uint32_t sample0;
         int batch_samples;
@@ -187,7 +188,7 @@ namespace wost
         WalkState<D> w;
         NearestTrav<D> t;
         uint32_t depth = 0;
-        bool has_walk = false, exhausted = false, trav = false;
+        bool has_walk = false, exhausted = false, trav = false, fresh = false;
         unsigned int my_steps = 0;
         float bound = dm_inf(); // upper bound of the next closest-point distance: R_D of this step + the distance moved
         w.pixel = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
@@ -229,7 +230,8 @@ namespace wost
                         if (i < njobs)
                         {
                             const uint32_t sj = (uint32_t)(i / a.n_active);
-                            w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
+                            const long long ai = i - (long long)sj * a.n_active;
+                            w.pixel = __ldg(a.active + ai);
                             w.sample = a.sample0 + sj;
                             w.x = eval_point(c, w.pixel);
                             w.thp = 1.0f;
@@ -240,6 +242,12 @@ namespace wost
                             depth = 0;
                             has_walk = true;
                             bound = dm_inf();
+                            // every sample of a pixel starts at the same point: its closest-point query was answered once
+                            // per solve by k_first_hit (same traversal, same bits)
+                            const uint2 f = __ldg(a.first + ai);
+                            t.win = f.x;
+                            t.best = __uint_as_float(f.y);
+                            fresh = true;
                         }
                         else
                             exhausted = true;
@@ -248,7 +256,10 @@ namespace wost
                 if (!trav && has_walk)
                 {
                     ++my_steps;
-                    trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t, bound);
+                    if (fresh)
+                        fresh = false; // result already in t: the lane stays pending and takes the next tail phase
+                    else
+                        trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t, bound);
                 }
             }
             else if (trav_mask == 0u)
@@ -465,6 +476,17 @@ namespace wost
             WOST_CUDA_TRY(cudaEventCreate(&e));
             it->batch_ev.push_back(e);
         }
+        if (nbatches > 0)
+        {
+            if (it->d_first.count < (size_t)it->n_active && it->d_first.alloc((size_t)it->n_active) != cudaSuccess)
+            {
+                set_last_error("wost_solve: first-hit cache allocation failed");
+                return WOST_ERR_CUDA;
+            }
+            const int grid = std::max(1, std::min(grid_full, div_up(it->n_active, kWalkBlock)));
+            k_first_hit<D, RefOrder><<<grid, kWalkBlock, smem, st>>>(ctx, it->d_active.ptr, it->n_active, it->d_first.ptr, it->d_overflow.ptr);
+            ++it->launches;
+        }
         for (int s0 = 0, bi = 0; bi < nbatches; s0 += S, ++bi)
         {
             const int Sb = std::min(S, spp - s0);
@@ -472,6 +494,7 @@ namespace wost
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi], st));
             PersistArgs a;
             a.active = it->d_active.ptr;
+            a.first = it->d_first.ptr;
             a.n_active = it->n_active;
             a.sample0 = (uint32_t)s0;
             a.batch_samples = Sb;

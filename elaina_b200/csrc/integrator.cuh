@@ -29,6 +29,7 @@ struct wost_integrator
     int spp_batch = 1; // S: samples of every pixel in flight per wavefront
     size_t queue_capacity = 0;
     wost::DevBuf<uint32_t> d_active;
+    wost::DevBuf<uint2> d_first; // per active pixel: closest-point result of the evaluation point {leaf position, re-squared distance}
     wost::DevBuf<float4> qa[2], qb[2];
     wost::DevBuf<uint32_t> qc[2];
     wost::DevBuf<int> d_counts; // [0..max_depth]: items of bounce d; [max_depth+1 ..]: claim cursors

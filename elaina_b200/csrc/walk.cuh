@@ -227,7 +227,9 @@ namespace wost
         {
             const float x = (w3[k] - c.source_origin[k]) * c.source_inv_voxel;
             const float fl = floorf(x);
-            ijk[k] = (int)fl;
+            // clamp before the conversion: walks that escape an exterior problem reach |x| ~ 1e19, where (int)fl saturates to
+            // INT_MAX and `ijk + 1` wraps (signed overflow: the bounds test below may then be folded into `true`)
+            ijk[k] = (int)fminf(fmaxf(fl, -2.0f), 1.0e9f);
             f[k] = x - fl;
         }
 #pragma unroll
@@ -543,4 +545,34 @@ namespace wost
             return false;
         return walk_step_tail<D>(c, w, depth, st, acc, R_D, pos);
     }
+    // Closest-point query of every active evaluation point, once per solve. All samples of a pixel start their walk at
+    // the same point (generateEvaluationPointsImpl, integrator.cu:80-100), and that first query is the most expensive of
+    // the walk (deep interior, no a-priori bound): the walk kernels read its result instead of repeating it per sample.
+    template <int D, bool RefOrder>
+    __global__ void __launch_bounds__(128) k_first_hit(const __grid_constant__ WalkCtx<D> c, const uint32_t *active, int n_active, uint2 *first, int *overflow)
+    {
+        extern __shared__ uint2 smem_stack[];
+        SmemStack st;
+        uint2 spill_mem[kSpillLevels];
+        st.init(smem_stack, overflow, spill_mem);
+        for (int base = blockIdx.x * blockDim.x; base < n_active; base += gridDim.x * blockDim.x)
+        {
+            const int i = base + threadIdx.x;
+            const bool valid = i < n_active;
+            const Vec<D> x = eval_point(c, valid ? __ldg(active + i) : 0u);
+            NearestTrav<D> t;
+            t.win = kInvalid, t.best = dm_inf();
+            bool trav = false;
+            if (valid)
+                trav = nearest_begin<D, RefOrder>(c.dir, x, st, t);
+            while (__any_sync(kFullMask, trav))
+            {
+                if (trav)
+                    trav = nearest_trip<D, RefOrder>(c.dir, x, st, t);
+            }
+            if (valid)
+                first[i] = make_uint2(t.win, __float_as_uint(t.best));
+        }
+    }
+
 } // namespace wost

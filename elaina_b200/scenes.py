@@ -101,6 +101,36 @@ def star_polygon(nseg=10000, r0=1.0, amp=0.3, lobes=5):
     return verts, prims
 
 
+def stroke_soup(nstrokes=60, nseg=1024, lo=30.0, hi=470.0, seed=11):
+    """C1 stand-in (data/ladybug/model.obj is a soup of 61 476 open diffusion-curve strokes inside a 500x500 Neumann
+    square): `nstrokes` open polylines of `nseg` segments each, smooth random-walk headings, reflected into [lo, hi]^2."""
+    rng = np.random.RandomState(seed)
+    verts, prims = [], []
+    base = 0
+    for _ in range(nstrokes):
+        length = rng.uniform(150.0, 500.0)
+        step = length / nseg
+        k = rng.randn(3) * 6.0 / nseg
+        ph = rng.rand(3) * 2.0 * math.pi
+        i = np.arange(nseg + 1, dtype=np.float64)
+        heading = rng.rand() * 2.0 * math.pi + 1.5 * (np.sin(k[0] * i * 3 + ph[0]) + np.sin(k[1] * i * 5 + ph[1]) + 0.5 * np.sin(k[2] * i * 11 + ph[2]))
+        xy = np.cumsum(np.stack([np.cos(heading), np.sin(heading)], 1) * step, 0) + rng.uniform(lo + 60.0, hi - 60.0, 2)
+        span = hi - lo  # fold (reflect) the curve back into the box
+        xy = np.abs(np.mod(xy - lo, 2.0 * span) - span)
+        xy = lo + span - xy
+        verts.append(xy)
+        idx = np.arange(nseg, dtype=np.int32) + base
+        prims.append(np.stack([idx, idx + 1], 1))
+        base += nseg + 1
+    return np.concatenate(verts, 0).astype(np.float32), np.concatenate(prims, 0).astype(np.int32)
+
+
+def stroke_colors(nstrokes, nseg, seed=7):
+    """Piecewise-constant left/right colour pairs per stroke of `stroke_soup` (stand-in for the missing color.json)."""
+    table = np.random.RandomState(seed).rand(nstrokes, 6).astype(np.float32)
+    return np.repeat(table, nseg + 1, axis=0)
+
+
 def harmonic_2d(xy, n=3):
     """Re(z^n): harmonic in the plane."""
     z = xy[..., 0].astype(np.float64) + 1j * xy[..., 1].astype(np.float64)

@@ -251,7 +251,7 @@ namespace
         {
             const float x = (w3[k] - p.source_origin[k]) * inv;
             const float fl = floorf(x);
-            ijk[k] = (int)fl;
+            ijk[k] = (int)fminf(fmaxf(fl, -2.0f), 1.0e9f); // far outside the grid: stay clear of INT_MAX + 1
             f[k] = x - fl;
         }
         auto fetch = [&](int i, int j, int k, int ch) -> float

@@ -125,6 +125,30 @@ def test_sdf_channels_match_queries(oracle):
     assert np.array_equal(bits(it.film(api.CH_NEUMANN_SDF)[..., 0].ravel()), bits(sd))
 
 
+def test_source_lookup_far_outside_the_grid(oracle):
+    """Walks of an exterior problem escape to |x| ~ 1e19; the source lookup there must read zero, not wrap its voxel index
+    (regression: illegal address on the 3D Poisson bench scene). Directed: the SOURCE channel on a 1e12-wide evaluation grid,
+    then an exterior 3D solve against the oracle."""
+    from elaina_b200 import api, scenes
+    dv, dp = scenes.icosphere(2, 1.0, 0.1)
+    spec = dict(dim=3, dverts=dv, dprims=dp, color_dirichlet=scenes.gray_pairs(scenes.harmonic_3d(dv)),
+                source=np.ones((16, 16, 16, 3), np.float32), source_origin=(-1.6, -1.6, -1.6), source_voxel=0.2,
+                grid_scale=1.0e12, grid_pos=(0.37e12, 0.0, 0.0), grid_up=(0.0, 1.0, 0.0), grid_right=(1.0, 0.0, 0.0))
+    oprob, gprob = build_both(oracle, spec)
+    it = api.UniformIntegrator(gprob, api.make_settings((32, 32), 8, 1, 5e-3))
+    it.renderSource()
+    src = it.film(api.CH_SOURCE)[..., :3]
+    assert np.all(src == 0.0)
+    spec["grid_scale"] = 3.0  # most pixels lie outside the sphere: exterior walks, star radii grow geometrically
+    oprob, gprob = build_both(oracle, spec)
+    st = _settings(24, 24, 64, 8, 1e-2, 9)
+    sol_o, steps_o = oracle.solve_uniform(oprob, st)
+    it = api.UniformIntegrator(gprob, api.make_settings((24, 24), 64, 8, 1e-2, seed=9))
+    it.solve()
+    assert it.last_walk_steps == steps_o
+    assert np.array_equal(bits(it.film()[..., :3].reshape(-1, 3)), bits(sol_o))
+
+
 def test_sharding_is_invisible():
     """Pixel-keyed RNG: two shards (interleaved rows) reproduce the single-handle film exactly."""
     from elaina_b200 import api
