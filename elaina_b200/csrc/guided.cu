@@ -185,7 +185,7 @@ namespace wost
     // (profiles/r1_notes.md), refilling keeps the traversal -- the bulk of the instructions -- near full width.
     // First: items are synthesised from (pixel, sample) = generateEvaluationPointsImpl (integrator.cu:131-151).
     constexpr int kGRefill = 6;
-    template <int D, bool First>
+    template <int D, bool First, int F>
     __global__ void __launch_bounds__(kGBlock) k_g_arrive(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
     {
         extern __shared__ uint2 smem_stack[];
@@ -216,7 +216,7 @@ namespace wost
                     PixelAccT<true> acc;
                     acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
                     acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
-                    on = walk_step_contrib<D>(c, it.w, a.depth, st, acc, nearest_distance(t), t.win, 1.0f, it.R_B);
+                    on = walk_step_contrib<D, F>(c, it.w, a.depth, st, acc, nearest_distance(t), t.win, 1.0f, it.R_B);
                     acc.flush();
                     it.T[0] = acc.tot[0], it.T[1] = acc.tot[1], it.T[2] = acc.tot[2];
                     if (!on)
@@ -421,7 +421,7 @@ namespace wost
     // Same persistent-lane scheme as k_g_arrive, but a lane keeps its walk until it ends: tail phase = contribution
     // stages of the point just reached, then uniform direction + walk record + move; lanes without a walk claim the
     // next out-shell item of the queue.
-    template <int D>
+    template <int D, int F>
     __global__ void __launch_bounds__(kGBlock) k_g_finish(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
     {
         extern __shared__ uint2 smem_stack[];
@@ -454,7 +454,7 @@ namespace wost
                     acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
                     acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
                     rd = nearest_distance(t);
-                    const bool on = walk_step_contrib<D>(c, it.w, depth, st, acc, rd, t.win, 1.0f, it.R_B);
+                    const bool on = walk_step_contrib<D, F>(c, it.w, depth, st, acc, rd, t.win, 1.0f, it.R_B);
                     acc.flush();
                     it.T[0] = acc.tot[0], it.T[1] = acc.tot[1], it.T[2] = acc.tot[2];
                     need_contrib = false;
@@ -490,13 +490,13 @@ namespace wost
                 if (!trav && has)
                 {
                     float pdf;
-                    const Vec<D> dir = uniform_direction<D>(c, it.w, depth, pdf);
+                    const Vec<D> dir = uniform_direction<D, F>(c, it.w, depth, pdf);
                     if (a.training && depth < (uint32_t)a.max_train_depth)
                         g_record<D>(a, it, dir, pdf, depth);
                     if ((int)depth + 1 < a.max_depth)
                     {
                         const Vec<D> x0 = it.w.x;
-                        walk_advance<D>(c, it.w, dir, pdf, it.R_B, st);
+                        walk_advance<D, F>(c, it.w, dir, pdf, it.R_B, st);
                         ++depth;
                         ++my_steps;
                         need_contrib = true;
@@ -1317,8 +1317,20 @@ namespace wost
         return WOST_OK;
     }
 
+    template <int D, int F>
+    static wost_status solve_guided_f(wost_integrator *it, uint64_t *walk_steps);
+    // arrive / finish kernels compiled for the features the problem has (walk.cuh: kFeatNeumann / kFeatSource)
     template <int D>
     static wost_status solve_guided_impl(wost_integrator *it, uint64_t *walk_steps)
+    {
+        if (it->problem->neumann != nullptr)
+            return solve_guided_f<D, kFeatAll>(it, walk_steps);
+        if (it->problem->d_source.ptr != nullptr)
+            return solve_guided_f<D, kFeatSource>(it, walk_steps);
+        return solve_guided_f<D, 0>(it, walk_steps);
+    }
+    template <int D, int F>
+    static wost_status solve_guided_f(wost_integrator *it, uint64_t *walk_steps)
     {
         if (!it->net)
         {
@@ -1335,7 +1347,7 @@ namespace wost
         const int S = it->spp_batch;
         const size_t stack_smem = stack_smem_bytes(kGBlock);
         int occ = 1;
-        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_arrive<D, false>, kGBlock, stack_smem));
+        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_arrive<D, false, F>, kGBlock, stack_smem));
         const int grid_full = sm_count() * std::max(1, occ);
         int grid_bounce = sm_count();
         WOST_DISPATCH_K0(D, n.k0, (grid_bounce = bounce_grid<D, K0_>()));
@@ -1421,7 +1433,7 @@ namespace wost
                 const long long n0 = (long long)it->n_active * Sb;
                 const int grid = (int)std::min<long long>(grid_full, (n0 + kGBlock - 1) / kGBlock);
                 prof_mark(0);
-                k_g_arrive<D, true><<<std::max(1, grid), kGBlock, stack_smem, st>>>(ctx, a);
+                k_g_arrive<D, true, F><<<std::max(1, grid), kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }
             // out-shell items of depth d live in queue d & 1
@@ -1444,7 +1456,7 @@ namespace wost
                     a.in = queue(d & 1), a.out = queue((d + 1) & 1);
                     a.in_count = counts + d, a.out_count = counts + d + 1, a.cursor = cur_a + d + 1, a.depth = (uint32_t)(d + 1);
                     prof_mark(0);
-                    k_g_arrive<D, false><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
+                    k_g_arrive<D, false, F><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
                     ++it->launches, ++it->step_launches;
                 }
             }
@@ -1453,7 +1465,7 @@ namespace wost
                 a.in = queue(G & 1), a.out = queue((G + 1) & 1);
                 a.in_count = counts + G, a.out_count = nullptr, a.cursor = cur_b + G, a.depth = (uint32_t)G;
                 prof_mark(2);
-                k_g_finish<D><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
+                k_g_finish<D, F><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }
             prof_mark(3);

@@ -176,7 +176,7 @@ namespace wost
         int *overflow;
     };
 
-    template <int D, bool RefOrder>
+    template <int D, bool RefOrder, int F>
     __global__ void __launch_bounds__(kWalkBlock) k_walk_persistent(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ PersistArgs a)
     {
         extern __shared__ uint2 smem_stack[];
@@ -208,7 +208,7 @@ namespace wost
                     acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
                     const Vec<D> x0 = w.x;
                     const float R_D = nearest_distance(t);
-                    const bool alive = walk_step_tail<D>(c, w, depth, st, acc, R_D, t.win);
+                    const bool alive = walk_step_tail<D, F>(c, w, depth, st, acc, R_D, t.win);
                     acc.flush();
                     ++depth;
                     if (!alive || depth >= (uint32_t)a.max_depth)
@@ -444,8 +444,24 @@ namespace wost
         }
         return WOST_OK;
     }
+    template <int D, bool RefOrder, int F>
+    static wost_status solve_persistent_f(wost_integrator *it, uint64_t *walk_steps);
+    // picks the kernel variant compiled for the features this problem has (walk.cuh: kFeatNeumann / kFeatSource); the
+    // reference-order stand-in mode always runs the full-feature variant
     template <int D, bool RefOrder>
     static wost_status solve_persistent(wost_integrator *it, uint64_t *walk_steps)
+    {
+        if (RefOrder)
+            return solve_persistent_f<D, RefOrder, kFeatAll>(it, walk_steps);
+        const bool neu = it->problem->neumann != nullptr, src = it->problem->d_source.ptr != nullptr;
+        if (neu)
+            return solve_persistent_f<D, false, kFeatAll>(it, walk_steps);
+        if (src)
+            return solve_persistent_f<D, false, kFeatSource>(it, walk_steps);
+        return solve_persistent_f<D, false, 0>(it, walk_steps);
+    }
+    template <int D, bool RefOrder, int F>
+    static wost_status solve_persistent_f(wost_integrator *it, uint64_t *walk_steps)
     {
         WalkCtx<D> ctx;
         it->problem->fill_ctx(ctx);
@@ -459,7 +475,7 @@ namespace wost
         cudaStream_t st = it->stream;
         const size_t smem = stack_smem_bytes(kWalkBlock);
         int occ = 1;
-        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_walk_persistent<D, RefOrder>, kWalkBlock, smem));
+        WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_walk_persistent<D, RefOrder, F>, kWalkBlock, smem));
         const int grid_full = sm_count() * std::max(1, occ);
         int refill_threshold = kRefillThreshold;
         if (const char *e = getenv("WOST_REFILL_THRESHOLD")) // tuning knob (profiles/r1_notes.md)
@@ -507,7 +523,7 @@ namespace wost
             a.overflow = it->d_overflow.ptr;
             const long long n0 = (long long)it->n_active * Sb;
             const int grid = (int)std::min<long long>(grid_full, (n0 + kWalkBlock - 1) / kWalkBlock);
-            k_walk_persistent<D, RefOrder><<<std::max(1, grid), kWalkBlock, smem, st>>>(ctx, a);
+            k_walk_persistent<D, RefOrder, F><<<std::max(1, grid), kWalkBlock, smem, st>>>(ctx, a);
             ++it->launches;
             ++it->step_launches;
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));

@@ -230,8 +230,8 @@ namespace wost
     // Shared-memory stack, one column per thread: entry(level, tid) = base[level * blockDim + tid].
     // Consecutive lanes hit consecutive 8-byte slots -> conflict-free. The first kSmemLevels levels live in shared memory, deeper ones
     // (real scenes need <= 26 in total) spill to local memory; beyond 64 (the reference's limit) a flag is raised.
-    constexpr int kSmemLevels = 32; // short stack in shared memory
-    constexpr int kSpillLevels = 32; // deeper levels spill to local memory (reference limit: 64 in total)
+    constexpr int kSmemLevels = 24; // short stack in shared memory (24 KB per 128-thread CTA: 9 CTAs per SM)
+    constexpr int kSpillLevels = 40; // deeper levels spill to local memory (reference limit: 64 in total)
     struct StackEntry
     {
         uint32_t ref;
@@ -607,16 +607,21 @@ namespace wost
         }
         return ret;
     }
+    // bound: the caller only uses min(bound, result) (the walker: R_B = min(R_D, R_N), integrator.cu:186-195), so the search
+    // starts with best = bound: subtrees and leaf children farther than that are skipped before their cone test (acos / asin /
+    // atan2 per child). Silhouettes closer than the bound are found exactly as without it -- the result is the minimum over the
+    // candidates that pass the (node-local) cone tests, independent of the visit order -- and when there is none the function
+    // returns the bound itself. bound = inf is the reference's query.
     template <int D>
-    WOST_DEV float query_silhouette(const DevBVH<D> &bvh, const Vec<D> &q, bool flip, SmemStack &st)
+    WOST_DEV float query_silhouette(const DevBVH<D> &bvh, const Vec<D> &q, bool flip, SmemStack &st, float bound = dm_inf())
     {
-        float best = dm_inf();
+        float best = bound;
         if (bvh.nprims <= 0)
             return best;
         if (bvh.nprims == 1)
         {
             float d = dm_inf();
-            if (bvh.root_cone[D] >= 0.0f && leaf_sil_distance(bvh, 0, q, dm_inf(), d, flip))
+            if (bvh.root_cone[D] >= 0.0f && leaf_sil_distance(bvh, 0, q, dm_inf(), d, flip) && d <= best)
                 best = d;
             return best;
         }
@@ -641,8 +646,9 @@ namespace wost
             Cone<D> lc, rc;
             load_cnode(bvh.cnodes + node, lc, rc);
             const float Lmin = box_mindist(n.lb, q), Rmin = box_mindist(n.rb, q);
-            const bool hitL = lc.half_angle >= 0.0f && cone_overlap(lc, q, n.lb, Lmin);
-            const bool hitR = rc.half_angle >= 0.0f && cone_overlap(rc, q, n.rb, Rmin);
+            const float best2 = best * best;
+            const bool hitL = lc.half_angle >= 0.0f && Lmin <= best2 && cone_overlap(lc, q, n.lb, Lmin);
+            const bool hitR = rc.half_angle >= 0.0f && Rmin <= best2 && cone_overlap(rc, q, n.rb, Rmin);
             bool pushL = false;
             if (hitL)
             {

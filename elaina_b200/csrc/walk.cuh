@@ -304,6 +304,11 @@ namespace wost
     };
     using PixelAcc = PixelAccT<false>;
 
+    // Problem features a kernel instantiation is compiled for: the host picks the leanest variant the problem allows
+    // (no Neumann mesh -> no silhouette query, no ray casts, no hemisphere sampling; no source grid -> no Green's-function
+    // sample), which cuts registers and the instruction footprint of the walk kernels.
+    constexpr int kFeatNeumann = 1, kFeatSource = 2, kFeatAll = 3;
+
     // ---------------------------------------------------------------------------------------------------------
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
     // Everything of a walk step that follows the closest-point query on the Dirichlet mesh (R_D, leaf position pos).
@@ -311,11 +316,13 @@ namespace wost
     // (epsilon-shell hit or no star radius); otherwise R_B holds the star radius of the step.
     // rb_scale: 0.99 in the uniform integrator (integrator/uniform/integrator.cu:193-195), 1 in the guided one
     // (integrator/guided/integrator.cu:238-239).
-    template <int D, class Acc>
+    template <int D, int F = kFeatAll, class Acc>
     WOST_DEV bool walk_step_contrib(const WalkCtx<D> &c, const WalkState<D> &w, uint32_t depth, SmemStack &st, Acc &acc, float R_D, uint32_t pos,
                                     float rb_scale, float &R_B)
     {
         const float eps = c.eps;
+        const bool has_neu = (F & kFeatNeumann) && c.neu.nprims > 0, has_src = (F & kFeatSource) && c.source != nullptr;
+        const bool onN = (F & kFeatNeumann) && w.onN;
         // ---- separate (integrator/uniform/integrator.cu:102-212)
         if (c.dir.nprims > 0)
         {
@@ -341,20 +348,20 @@ namespace wost
             }
         }
         float R_N = dm_inf();
-        if (c.neu.nprims > 0)
-            R_N = query_silhouette(c.neu, w.x, false, st);
+        if (has_neu)
+            R_N = query_silhouette(c.neu, w.x, false, st, R_D); // only min(R_D, R_N) is used
         R_B = dm_fmax(1e-4f, dm_fmin(R_D, R_N));
         R_B *= rb_scale;
         if (dm_isinf(R_B))
             return false;
 
         // ---- source sample (integrator.cu:234-316)
-        if (c.source)
+        if (has_src)
         {
             const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_SOURCE_DIR, 0);
             Vec<D> dir;
             float dirPdf, alpha = 1.0f;
-            if (w.onN)
+            if (onN)
             {
                 dir = to_world(w.nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
                 dirPdf = Dims<D>::hemi_pdf();
@@ -366,7 +373,7 @@ namespace wost
                 dirPdf = Dims<D>::sphere_pdf();
             }
             float dist = R_B;
-            if (c.neu.nprims > 0)
+            if (has_neu)
             {
                 Vec<D> o;
 #pragma unroll
@@ -398,7 +405,7 @@ namespace wost
 
         // ---- Neumann boundary sample (integrator.cu:318-445). Skipped when every Neumann colour is zero:
         // the stage could then only add -0 to the pixel ("pure overhead there").
-        if (c.neu.nprims > 0 && c.neumann_flux_enabled)
+        if (has_neu && c.neumann_flux_enabled)
         {
             const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_NEUMANN, 0);
             const float u0 = u32_to_unit_float(q.x), u1 = u32_to_unit_float(q.y), u2 = u32_to_unit_float(q.z);
@@ -413,7 +420,7 @@ namespace wost
                 if (r < R_B && r > 0)
                 {
                     Vec<D> o = w.x;
-                    if (w.onN)
+                    if (onN)
                     {
 #pragma unroll
                         for (int k = 0; k < D; ++k)
@@ -433,7 +440,7 @@ namespace wost
                         int side = point_side(pr, w.x);
                         float uv[2];
                         proj_ratio(pr, y, uv);
-                        if (w.onN)
+                        if (onN)
                         {
                             const float dn = vdot(prim_normal(pr), w.nN);
                             side = (0.0f < dn) - (dn < 0.0f);
@@ -459,11 +466,12 @@ namespace wost
         return true;
     }
     // uniform direction of oneStepWalk (integrator.cu:447-470): sphere, or hemisphere about the Neumann normal
-    template <int D>
+    template <int D, int F = kFeatAll>
     WOST_DEV Vec<D> uniform_direction(const WalkCtx<D> &c, const WalkState<D> &w, uint32_t depth, float &pdf)
     {
+        const bool onN = (F & kFeatNeumann) && w.onN;
         const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_WALK, 0);
-        if (w.onN)
+        if (onN)
         {
             pdf = Dims<D>::hemi_pdf();
             return to_world(w.nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
@@ -472,14 +480,15 @@ namespace wost
         return sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
     }
     // second half of oneStepWalk (integrator.cu:472-526): move along dir by R_B or to the first Neumann hit, update thp
-    template <int D>
+    template <int D, int F = kFeatAll>
     WOST_DEV void walk_advance(const WalkCtx<D> &c, WalkState<D> &w, const Vec<D> &dir, float pdf, float R_B, SmemStack &st)
     {
         const float eps = c.eps;
+        const bool has_neu = (F & kFeatNeumann) && c.neu.nprims > 0, onN = (F & kFeatNeumann) && w.onN;
         {
             Vec<D> cur = w.x;
             float alpha = 1.0f;
-            if (w.onN)
+            if (onN)
             {
                 alpha = 0.5f;
 #pragma unroll
@@ -494,7 +503,7 @@ namespace wost
                 normal[k] = 0.0f;
             }
             bool hit = false;
-            if (c.neu.nprims > 0)
+            if (has_neu)
             {
                 const RayResult rr = query_ray<D, false>(c.neu, Ray<D>(cur, dir), R_B, st);
                 hit = rr.hit;
@@ -519,15 +528,15 @@ namespace wost
         }
     }
     // Everything of a UNIFORM walk step that follows the closest-point query on the Dirichlet mesh (R_D, leaf position pos).
-    template <int D, class Acc>
+    template <int D, int F = kFeatAll, class Acc>
     WOST_DEV bool walk_step_tail(const WalkCtx<D> &c, WalkState<D> &w, uint32_t depth, SmemStack &st, Acc &acc, float R_D, uint32_t pos, float rb_scale = 0.99f)
     {
         float R_B;
-        if (!walk_step_contrib<D>(c, w, depth, st, acc, R_D, pos, rb_scale, R_B))
+        if (!walk_step_contrib<D, F>(c, w, depth, st, acc, R_D, pos, rb_scale, R_B))
             return false;
         float pdf;
-        const Vec<D> dir = uniform_direction<D>(c, w, depth, pdf);
-        walk_advance<D>(c, w, dir, pdf, R_B, st);
+        const Vec<D> dir = uniform_direction<D, F>(c, w, depth, pdf);
+        walk_advance<D, F>(c, w, dir, pdf, R_B, st);
         return true;
     }
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
