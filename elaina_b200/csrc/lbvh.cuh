@@ -230,8 +230,8 @@ namespace wost
     // Shared-memory stack, one column per thread: entry(level, tid) = base[level * blockDim + tid].
     // Consecutive lanes hit consecutive 8-byte slots -> conflict-free. The first kSmemLevels levels live in shared memory, deeper ones
     // (real scenes need <= 26 in total) spill to local memory; beyond 64 (the reference's limit) a flag is raised.
-    constexpr int kSmemLevels = 24; // short stack in shared memory (24 KB per 128-thread CTA: 9 CTAs per SM)
-    constexpr int kSpillLevels = 40; // deeper levels spill to local memory (reference limit: 64 in total)
+    constexpr int kSmemLevels = 20; // short stack in shared memory (20 KB per 128-thread CTA: 11 CTAs per SM)
+    constexpr int kSpillLevels = 44; // deeper levels spill to local memory (reference limit: 64 in total)
     struct StackEntry
     {
         uint32_t ref;
