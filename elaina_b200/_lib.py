@@ -115,10 +115,12 @@ SYMBOLS = [
     ("wost_guided_train_batch", c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PP(c_float), c_void_p]),
     ("wost_vmm_eval", c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_u32, c_void_p, c_void_p, c_void_p]),
     ("wost_set_allreduce", c_int, [c_void_p, c_void_p, c_void_p]),
+    ("wost_set_frame_callback", c_int, [c_void_p, c_void_p, c_void_p]),
     ("wost_guided_last_profile", c_int, [c_void_p, c_void_p]),
     ("wost_guided_last_stats", c_int, [c_void_p, _PP(c_u64), _PP(c_u64), _PP(c_float)]),
 ]
 ALLREDUCE_FN = ctypes.CFUNCTYPE(c_int, c_void_p, c_void_p, c_u64, c_void_p)
+FRAME_FN = ctypes.CFUNCTYPE(None, c_void_p, c_int, c_int, c_u64, ctypes.POINTER(ctypes.c_float), c_int, c_int)
 
 _lib = None
 

@@ -244,6 +244,23 @@ class _Integrator:
         except Exception:
             pass
 
+    def set_frame_callback(self, fn):
+        """Progressive metrics (uniform/integrator.cu:577-609): fn(kind, sample_id, elapsed_ms, film[H, W, 5]) is called during
+        solve() for every sample index the settings' saveSppMetricsDuration / saveTimeMetricsDuration select (kind 0 / 1)."""
+        if fn is None:
+            self._frame_cb = None
+            check(_lib.load().wost_set_frame_callback(self.h, None, None))
+            return
+
+        def tramp(user, kind, sample_id, ms, film, w, h):
+            try:
+                fn(kind, sample_id, ms, np.ctypeslib.as_array(film, shape=(h, w, 5)).copy())
+            except Exception:
+                import traceback
+                traceback.print_exc()
+        self._frame_cb = _lib.FRAME_FN(tramp)
+        check(_lib.load().wost_set_frame_callback(self.h, ctypes.cast(self._frame_cb, c_void_p), None))
+
     def solve(self):
         """-> wall-clock ms (like the reference's solve()); walk steps / device ms kept on the object."""
         ms, steps, dms = c_u64(), c_u64(), c_float()

@@ -367,6 +367,37 @@ namespace
                 fail(WOST_ERR_CONFIG, "Unrecognized integrator channel: " + chs.at(i).as_string());
             channels.insert(c);
         }
+        // progressive metrics (uniform/integrator.cu:577-609): frames/<sampleId>.{exr,png}, frames_time/<ms>.{exr,png}
+        struct FrameSink
+        {
+            std::string dir;
+        } sink{out_dir};
+        if (s.save_spp_metrics_duration > 0 || s.save_time_metrics_duration > 0)
+        {
+            if (s.save_spp_metrics_duration > 0)
+                mkdirs(out_dir + "/frames");
+            if (s.save_time_metrics_duration > 0)
+                mkdirs(out_dir + "/frames_time");
+            ck(wost_set_frame_callback(
+                H.it,
+                [](void *user, int kind, int sample_id, uint64_t elapsed_ms, const float *film, int w, int h)
+                {
+                    const FrameSink *fs = static_cast<const FrameSink *>(user);
+                    std::vector<float> rgba((size_t)w * h * 4);
+                    for (size_t p = 0; p < (size_t)w * h; ++p)
+                        for (int k = 0; k < 4; ++k)
+                            rgba[p * 4 + k] = film[p * 5 + k] / film[p * 5 + 4]; // Film::save: pixel / weight
+                    const std::string stem = kind == 0 ? fs->dir + "/frames/" + std::to_string(sample_id) : fs->dir + "/frames_time/" + std::to_string(elapsed_ms);
+                    try
+                    {
+                        save_pair(stem, w, h, rgba);
+                    }
+                    catch (...)
+                    {
+                    }
+                },
+                &sink));
+        }
         uint64_t duration = 0, steps = 0;
         float dev_ms = 0.0f;
         bool solved = false;

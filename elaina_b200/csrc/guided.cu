@@ -1378,7 +1378,7 @@ namespace wost
         for (int s0 = 0; s0 < spp;)
         {
             const bool training = s0 < it->s.train_spp_count;
-            int Sb = training ? 1 : std::min(S, spp - s0);
+            int Sb = training ? 1 : it->frame_batch(s0, std::min(S, spp - s0)); // cut after every dumped sample index (progressive metrics)
             batches.emplace_back(s0, Sb);
             s0 += Sb;
         }
@@ -1479,6 +1479,12 @@ namespace wost
                     return rc;
             }
             prof_mark(3);
+            if (it->frame_cb)
+            {
+                const wost_status frc = emit_frames(it, s0 + Sb - 1);
+                if (frc != WOST_OK)
+                    return frc;
+            }
             // the accumulator slots are summed into slot 0 between batches of different sizes? No: slot s of every batch
             // adds to acc[s]; k_resolve sums all S slots at the end, so a training batch (1 sample) simply uses slot 0.
         }

@@ -297,6 +297,24 @@ namespace wost
         f[4] = 1.0f;
     }
 
+    wost_status emit_frames(wost_integrator *it, int sample_id)
+    {
+        const int kinds = it->frame_kinds(sample_id);
+        if (!kinds)
+            return WOST_OK;
+        cudaStream_t st = it->stream;
+        k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, it->spp_batch, it->d_acc.ptr, (float)(sample_id + 1), nullptr, it->film[WOST_CH_SOLUTION].ptr);
+        ++it->launches;
+        it->frame_host.resize((size_t)it->npix * 5);
+        WOST_CUDA_TRY(cudaMemcpyAsync(it->frame_host.data(), it->film[WOST_CH_SOLUTION].ptr, sizeof(float) * 5 * (size_t)it->npix, cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaStreamSynchronize(st));
+        const uint64_t ms = (uint64_t)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - it->solve_t0).count();
+        for (int kind = 0; kind < 2; ++kind)
+            if (kinds & (1 << kind))
+                it->frame_cb(it->frame_user, kind, sample_id, ms, it->frame_host.data(), it->s.frame_w, it->s.frame_h);
+        return WOST_OK;
+    }
+
     // renderDirichletSDF / renderSilhouetteSDF / renderSource (integrator/common.h:51-163)
     template <int D>
     __global__ void __launch_bounds__(kWalkBlock) k_render_channel(const __grid_constant__ WalkCtx<D> c, int channel, int npix, float *film, int *overflow)
@@ -485,7 +503,15 @@ namespace wost
         it->launches = 0;
         it->step_launches = 0;
         it->step_kernel_ms = 0.0f;
-        const int nbatches = it->n_active > 0 ? (spp + S - 1) / S : 0;
+        // sample batches: S at a time, cut right after every sample index the progressive metrics dump
+        std::vector<std::pair<int, int>> batches;
+        for (int s0 = 0; it->n_active > 0 && s0 < spp;)
+        {
+            const int Sb = it->frame_batch(s0, std::min(S, spp - s0));
+            batches.emplace_back(s0, Sb);
+            s0 += Sb;
+        }
+        const int nbatches = (int)batches.size();
         while ((int)it->batch_ev.size() < 2 * nbatches)
         {
             cudaEvent_t e;
@@ -503,9 +529,9 @@ namespace wost
             k_first_hit<D, RefOrder><<<grid, kWalkBlock, smem, st>>>(ctx, it->d_active.ptr, it->n_active, it->d_first.ptr, it->d_overflow.ptr);
             ++it->launches;
         }
-        for (int s0 = 0, bi = 0; bi < nbatches; s0 += S, ++bi)
+        for (int bi = 0; bi < nbatches; ++bi)
         {
-            const int Sb = std::min(S, spp - s0);
+            const int s0 = batches[bi].first, Sb = batches[bi].second;
             WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int), st));
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi], st));
             PersistArgs a;
@@ -527,6 +553,12 @@ namespace wost
             ++it->launches;
             ++it->step_launches;
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));
+            if (it->frame_cb)
+            {
+                const wost_status frc = emit_frames(it, s0 + Sb - 1);
+                if (frc != WOST_OK)
+                    return frc;
+            }
         }
         k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
         ++it->launches;
@@ -746,6 +778,7 @@ extern "C"
         if (!it)
             return WOST_ERR_INVALID;
         const auto t0 = std::chrono::high_resolution_clock::now();
+        it->solve_t0 = t0;
         WOST_CUDA_TRY(cudaEventRecord(it->ev0, it->stream));
         wost_status rc;
         if (it->kind == WOST_GUIDED)
@@ -777,6 +810,15 @@ extern "C"
             WOST_CUDA_TRY(cudaEventElapsedTime(&f, it->ev0, it->ev1));
             *device_ms = f;
         }
+        return WOST_OK;
+    }
+
+    wost_status wost_set_frame_callback(wost_integrator *it, wost_frame_fn fn, void *user)
+    {
+        if (!it)
+            return WOST_ERR_INVALID;
+        it->frame_cb = fn;
+        it->frame_user = user;
         return WOST_OK;
     }
 

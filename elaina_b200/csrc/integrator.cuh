@@ -3,6 +3,8 @@
 #include "guided.cuh"
 #include "problem.cuh"
 
+#include <chrono>
+
 namespace wost
 {
     // Work queue of walk states: "SoA of 128-bit lanes". Replaces WorkQueue<T>/SOA<T>
@@ -51,10 +53,37 @@ struct wost_integrator
     wost::DevBuf<unsigned long long> d_cursor64;
     wost_allreduce_fn allreduce = nullptr;
     void *allreduce_user = nullptr;
+    wost_frame_fn frame_cb = nullptr; // progressive metrics (frames/, frames_time/)
+    void *frame_user = nullptr;
+    std::vector<float> frame_host;
+    std::chrono::high_resolution_clock::time_point solve_t0;
     uint64_t train_samples = 0, train_steps = 0;
     float last_loss = 0.0f;
     std::vector<cudaEvent_t> prof_ev; // WOST_PROFILE=1
     float prof_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    // progressive metrics: is sample index `sid` one the reference dumps (uniform/integrator.cu:577-609)? bit 0 spp, bit 1 time
+    int frame_kinds(int sid) const
+    {
+        if (!frame_cb)
+            return 0;
+        int k = 0;
+        if (s.save_spp_metrics_duration > 0 && sid % s.save_spp_metrics_duration == 0 && sid < s.save_spp_metrics_until)
+            k |= 1;
+        if (s.save_time_metrics_duration > 0 && sid % s.save_time_metrics_duration == 0)
+            k |= 2;
+        return k;
+    }
+    // largest batch [s0, s0 + n) with n <= want that ends right after the next dumped sample index (or want if none)
+    int frame_batch(int s0, int want) const
+    {
+        if (!frame_cb)
+            return want;
+        for (int i = 0; i < want; ++i)
+            if (frame_kinds(s0 + i))
+                return i + 1;
+        return want;
+    }
 
     ~wost_integrator()
     {
@@ -70,3 +99,9 @@ struct wost_integrator
             cudaStreamDestroy(stream);
     }
 };
+
+namespace wost
+{
+    // progressive metrics: resolve solution / (sample_id + 1), download, hand to the frame callback (no-op when sample_id is not dumped)
+    wost_status emit_frames(wost_integrator *it, int sample_id);
+}

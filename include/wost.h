@@ -204,6 +204,15 @@ extern "C"
      * callback must enqueue a SUM all-reduce on `stream` (a cudaStream_t) and return 0. */
     typedef int (*wost_allreduce_fn)(void *user, void *d_buf, uint64_t n_floats, void *stream);
     wost_status wost_set_allreduce(wost_integrator *it, wost_allreduce_fn fn, void *user);
+
+    /* Progressive metrics (integrator/uniform/integrator.cu:577-609, "frames/<sampleId>" and "frames_time/<ms>"): when
+     * settings.save_spp_metrics_duration > 0 or save_time_metrics_duration > 0, wost_solve() hands the running estimate
+     * solution / (sample_id + 1) to this callback after every sample index the reference would dump
+     * (sample_id % duration == 0 [and sample_id < save_spp_metrics_until for kind 0]). kind: 0 = spp metric, 1 = time
+     * metric. film: frame_w*frame_h*5 floats {r,g,b,a,weight}, host memory owned by the library, valid during the call.
+     * The solver cuts its sample batches at those indices, so a dump costs one stream synchronisation, as in the reference. */
+    typedef void (*wost_frame_fn)(void *user, int kind, int sample_id, uint64_t elapsed_ms, const float *film, int frame_w, int frame_h);
+    wost_status wost_set_frame_callback(wost_integrator *it, wost_frame_fn fn, void *user);
     /* with WOST_PROFILE=1 in the environment: device ms of the last guided solve by kernel class
      * [0] arrive (closest point + contributions), [1] bounce (MLP + sampling + move), [2] finish (uniform tail),
      * [3] gaps between classes, [4] training frames (samples + forward/backward + optimiser), [5..7] unused */

@@ -166,3 +166,39 @@ def test_guided_config_run(tmp_path):
     assert _run(pu)[0] == 0
     ref = _read_exr(tmp_path / "exp" / "u" / "solution.exr")
     assert abs(float(exr[..., :3].mean() - ref[..., :3].mean())) < 0.03
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("guided", [False, True])
+def test_progressive_frames(tmp_path, guided):
+    """saveSppMetricsDuration / saveSppMetricsUntil / saveTimeMetricsDuration (uniform/integrator.cu:577-609):
+    frames/<sampleId>.{exr,png} hold solution / (sampleId + 1) for sampleId % duration == 0 and sampleId < until;
+    frames_time/<ms>.* likewise for the time metric. The last frame of a run equals a shorter run's solution."""
+    from elaina_b200 import api
+    p, conf, (dv, dp, nv, npr, cols) = _write_scene(tmp_path, guided=guided)
+    conf["integrator"]["setting"].update({"saveSppMetricsDuration": 3, "saveSppMetricsUntil": 7, "saveTimeMetricsDuration": 4})
+    p.write_text(json.dumps(conf, indent=4))
+    rc, msg = _run(p)
+    assert rc == 0, msg
+    out = tmp_path / "exp" / ("g" if guided else "u")
+    assert sorted(os.listdir(out / "frames")) == ["0.exr", "0.png", "3.exr", "3.png", "6.exr", "6.png"]   # 8 spp: ids 0, 3, 6 (< 7)
+    assert len([f for f in os.listdir(out / "frames_time") if f.endswith(".exr")]) in (1, 2)         # ids 0 and 4 (same ms -> same name)
+    f6 = _read_exr(out / "frames" / "6.exr")
+    assert np.isfinite(f6).all() and f6[..., 3].min() == 1.0
+    if not guided:
+        # the frame after sample 6 is the 7-spp estimate of the same Philox streams
+        prob = api.Problem(2, dirichlet=api.Scene(2, dv, dp), neumann=api.Scene(2, nv, npr), color_dirichlet=cols,
+                           grid_scale=200.0, grid_pos=(250.0, 250.0), grid_up=(-1.0, 0.0), aabb_min=(0.0, 0.0), aabb_max=(500.0, 500.0))
+        st = dict(conf["integrator"]["setting"], samplesPerPixel=7, saveSppMetricsDuration=-1, saveTimeMetricsDuration=-1)
+        it = api.UniformIntegrator(prob, api.settings_from_json(st, seed=7))
+        it.solve()
+        film = it.film()
+        want = (film[..., :4] / film[..., 4:5])[::-1]
+        np.testing.assert_allclose(f6, want, rtol=2e-3, atol=2e-3)
+        # and the callback surface of the API delivers the same frames
+        got = []
+        it2 = api.UniformIntegrator(prob, api.settings_from_json(conf["integrator"]["setting"], seed=7))
+        it2.set_frame_callback(lambda kind, sid, ms, film: got.append((kind, sid, film)))
+        it2.solve()
+        assert [(k, s) for k, s, _ in got] == [(0, 0), (1, 0), (0, 3), (1, 4), (0, 6)]
+        np.testing.assert_allclose((got[-1][2][..., :4] / got[-1][2][..., 4:5])[::-1], f6, rtol=2e-3, atol=2e-3)
