@@ -13,6 +13,7 @@
 #include "scene.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include <algorithm>
 #include <mutex>
@@ -771,6 +772,119 @@ namespace wost
         }
     }
 
+    // ------------------------------------------------------------------ device: edge adjacency of a triangle mesh
+    // Replaces the reference's host loops over std::map / std::unordered_map (scene.cuh:1135-1229; seconds at 10^6
+    // triangles) with sort-by-edge-key. Slot = 3 * triangle + local edge. Same results as the sequential code:
+    //   edge ids     in first-seen order            -> rank of the edge's first slot among all first slots (scan)
+    //   record write "last triangle wins" per field -> the slots of one edge are replayed in ascending order by one thread
+    //   ownership    first triangle that references -> the edge's first slot
+    __global__ void k_edge_keys(int nprims, const int *prims, unsigned long long *keys, int *slots)
+    {
+        const int sl = blockIdx.x * blockDim.x + threadIdx.x;
+        if (sl >= 3 * nprims)
+            return;
+        const int i = sl / 3, j = sl - 3 * i;
+        int I = prims[3 * i + j], J = prims[3 * i + (j + 1) % 3];
+        if (I > J)
+        {
+            const int t = I;
+            I = J;
+            J = t;
+        }
+        keys[sl] = ((unsigned long long)(uint32_t)I << 32) | (uint32_t)J;
+        slots[sl] = sl;
+    }
+    __global__ void k_edge_heads(int nslots, const unsigned long long *skeys, const int *sslots, int *first_flag)
+    {
+        const int p = blockIdx.x * blockDim.x + threadIdx.x;
+        if (p >= nslots)
+            return;
+        if (p == 0 || skeys[p] != skeys[p - 1])
+            first_flag[sslots[p]] = 1; // stable sort: the first slot of the run is the smallest one
+    }
+    __global__ void k_edge_records(int nslots, const unsigned long long *skeys, const int *sslots, const int *first_rank, const int *prims, int *eot, int *sil_rec)
+    {
+        const int p = blockIdx.x * blockDim.x + threadIdx.x;
+        if (p >= nslots || (p > 0 && skeys[p] == skeys[p - 1]))
+            return;
+        const int e = first_rank[sslots[p]];
+        int *rec = sil_rec + (size_t)e * 4;
+        int r0 = -1, r1 = -1, r2 = -1, r3 = -1;
+        for (int q = p; q < nslots && skeys[q] == skeys[p]; ++q)
+        {
+            const int sl = sslots[q];
+            eot[sl] = e;
+            const int i = sl / 3, j = sl - 3 * i;
+            const int I = j - 1 < 0 ? 2 : j - 1;
+            int J = j, K = j + 1 > 2 ? 0 : j + 1;
+            int orientation = 1;
+            if (prims[3 * i + J] > prims[3 * i + K])
+            {
+                const int t = J;
+                J = K;
+                K = t;
+                orientation = -1;
+            }
+            if (orientation == 1)
+                r0 = prims[3 * i + I];
+            else
+                r3 = prims[3 * i + I];
+            r1 = prims[3 * i + J];
+            r2 = prims[3 * i + K];
+        }
+        rec[0] = r0, rec[1] = r1, rec[2] = r2, rec[3] = r3;
+    }
+    __global__ void k_prim_edges(int nprims, const int *first_flag, const int *eot, int *prim_sil)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= nprims)
+            return;
+        int out[3] = {-1, -1, -1};
+        int ptr = 0;
+        for (int j = 0; j < 3; ++j)
+            if (first_flag[3 * i + j])
+                out[ptr++] = eot[3 * i + j];
+        prim_sil[3 * i] = out[0], prim_sil[3 * i + 1] = out[1], prim_sil[3 * i + 2] = out[2];
+    }
+    // fills s->d_sil_rec (E x 4), s->d_prim_sil (nprims x 3), s->nsil = E from s->d_prims
+    static wost_status device_silhouettes_3d(wost_scene *s)
+    {
+        const int n = s->nprims, ns = 3 * n, B = 256;
+        cudaStream_t st = 0;
+        DevBuf<unsigned long long> keys, skeys;
+        DevBuf<int> slots, sslots, first_flag, first_rank, eot;
+        DevBuf<char> temp;
+        WOST_CUDA_TRY(keys.alloc(ns));
+        WOST_CUDA_TRY(skeys.alloc(ns));
+        WOST_CUDA_TRY(slots.alloc(ns));
+        WOST_CUDA_TRY(sslots.alloc(ns));
+        WOST_CUDA_TRY(first_flag.alloc(ns));
+        WOST_CUDA_TRY(first_rank.alloc(ns));
+        WOST_CUDA_TRY(eot.alloc(ns));
+        k_edge_keys<<<div_up(ns, B), B, 0, st>>>(n, s->d_prims.ptr, keys.ptr, slots.ptr);
+        size_t tb1 = 0, tb2 = 0;
+        WOST_CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tb1, keys.ptr, skeys.ptr, slots.ptr, sslots.ptr, ns, 0, 64, st));
+        WOST_CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tb2, first_flag.ptr, first_rank.ptr, ns, st));
+        WOST_CUDA_TRY(temp.alloc(std::max(tb1, tb2)));
+        WOST_CUDA_TRY(cub::DeviceRadixSort::SortPairs(temp.ptr, tb1, keys.ptr, skeys.ptr, slots.ptr, sslots.ptr, ns, 0, 64, st));
+        WOST_CUDA_TRY(cudaMemsetAsync(first_flag.ptr, 0, sizeof(int) * (size_t)ns, st));
+        k_edge_heads<<<div_up(ns, B), B, 0, st>>>(ns, skeys.ptr, sslots.ptr, first_flag.ptr);
+        WOST_CUDA_TRY(cub::DeviceScan::ExclusiveSum(temp.ptr, tb2, first_flag.ptr, first_rank.ptr, ns, st));
+        int last_rank = 0, last_flag = 0;
+        WOST_CUDA_TRY(cudaMemcpyAsync(&last_rank, first_rank.ptr + (ns - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaMemcpyAsync(&last_flag, first_flag.ptr + (ns - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        WOST_CUDA_TRY(cudaStreamSynchronize(st));
+        const int E = last_rank + last_flag;
+        s->nsil = E;
+        WOST_CUDA_TRY(s->d_sil_rec.alloc((size_t)E * 4));
+        WOST_CUDA_TRY(s->d_prim_sil.alloc((size_t)n * 3));
+        k_edge_records<<<div_up(ns, B), B, 0, st>>>(ns, skeys.ptr, sslots.ptr, first_rank.ptr, s->d_prims.ptr, eot.ptr, s->d_sil_rec.ptr);
+        k_prim_edges<<<div_up(n, B), B, 0, st>>>(n, first_flag.ptr, eot.ptr, s->d_prim_sil.ptr);
+        WOST_CUDA_TRY(cudaStreamSynchronize(st));
+        WOST_CUDA_TRY(cudaGetLastError());
+        return WOST_OK;
+    }
+
     template <int D>
     static wost_status build_scene(wost_scene *s)
     {
@@ -1014,10 +1128,13 @@ extern "C"
         s->nprims = nprims;
         s->h_verts.assign(verts, verts + (size_t)nverts * dim);
         s->h_prims.assign(prims, prims + (size_t)nprims * dim);
+        // silhouette adjacency: vertices of a polyline on the host (two linear passes), edges of a triangle mesh on the device
+        // (WOST_HOST_SILHOUETTES=1 keeps the host hash-map path as a cross-check)
         std::vector<int> sil_rec, prim_sil;
+        const bool host_sil = dim == 2 || getenv("WOST_HOST_SILHOUETTES") != nullptr;
         if (dim == 2)
             host_silhouettes_2d(nverts, nprims, prims, sil_rec, prim_sil);
-        else
+        else if (host_sil)
             host_silhouettes_3d(nprims, prims, sil_rec, prim_sil);
         s->nsil = (int)sil_rec.size() / 4;
         wost_status rc = WOST_OK;
@@ -1027,10 +1144,16 @@ extern "C"
             return r;
         };
         if (s->d_verts.upload(verts, (size_t)nverts * dim) != cudaSuccess || s->d_prims.upload(prims, (size_t)nprims * dim) != cudaSuccess ||
-            s->d_sil_rec.upload(sil_rec.data(), sil_rec.size()) != cudaSuccess || s->d_prim_sil.upload(prim_sil.data(), prim_sil.size()) != cudaSuccess)
+            (host_sil && (s->d_sil_rec.upload(sil_rec.data(), sil_rec.size()) != cudaSuccess || s->d_prim_sil.upload(prim_sil.data(), prim_sil.size()) != cudaSuccess)))
         {
             set_last_error(std::string("wost_scene_create: upload failed: ") + cudaGetErrorString(cudaGetLastError()));
             return fail(WOST_ERR_CUDA);
+        }
+        if (!host_sil)
+        {
+            rc = device_silhouettes_3d(s);
+            if (rc != WOST_OK)
+                return fail(rc);
         }
         rc = (dim == 2) ? build_scene<2>(s) : build_scene<3>(s);
         if (rc != WOST_OK)

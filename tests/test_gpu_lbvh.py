@@ -143,3 +143,26 @@ def test_nearest_tie_breaks_and_far_queries(oracle, name):
         ig, dg = sg.nearest(q)
         assert np.array_equal(io, ig)
         assert np.array_equal(bits(do), bits(dg))
+
+
+@pytest.mark.gpu
+def test_device_edge_adjacency_equals_host_path(monkeypatch):
+    """Row N1: the triangle-mesh silhouette adjacency is built on the device (sort by edge key); the host hash-map path
+    (the reference's sequential semantics, scene.cuh:1135-1229) is kept behind WOST_HOST_SILHOUETTES as a cross-check.
+    Non-manifold soup (edges shared by > 2 triangles, both orientations) + a closed mesh; cones and silhouette distances equal."""
+    from elaina_b200 import api, scenes
+    rng = np.random.RandomState(5)
+    tri = rng.rand(300, 3).astype(np.float32)
+    tidx = rng.randint(0, 300, (4000, 3)).astype(np.int32)   # few vertices, many triangles: high edge valence
+    tidx = tidx[(tidx[:, 0] != tidx[:, 1]) & (tidx[:, 1] != tidx[:, 2]) & (tidx[:, 0] != tidx[:, 2])]
+    for verts, prims in ((tri, tidx), scenes.icosphere(5, 1.0, 0.2)):
+        q = (rng.rand(2000, 3).astype(np.float32) * 2.4 - 1.2)
+        monkeypatch.delenv("WOST_HOST_SILHOUETTES", raising=False)
+        dev = api.Scene(3, verts, prims)
+        monkeypatch.setenv("WOST_HOST_SILHOUETTES", "1")
+        host = api.Scene(3, verts, prims)
+        nd, bd, cd = dev.dump_bvh()
+        nh, bh, ch = host.dump_bvh()
+        assert np.array_equal(nd, nh) and np.array_equal(bits(bd), bits(bh)) and np.array_equal(bits(cd), bits(ch))
+        for flip in (False, True):
+            assert np.array_equal(bits(dev.silhouette(q, flip)), bits(host.silhouette(q, flip)))
