@@ -435,6 +435,7 @@ namespace wost
         uint32_t depth = a.depth;
         bool has = false, exhausted = false, trav = false, need_contrib = false;
         float rd = dm_inf(); // closest distance at the point the walk is about to leave (upper-bounds the next query)
+        bool win_known = false; // t.win is the closest primitive of the point the walk is about to leave
         unsigned int my_steps = 0;
         it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
         it.T[0] = it.T[1] = it.T[2] = 0.0f;
@@ -454,6 +455,7 @@ namespace wost
                     acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
                     acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
                     rd = nearest_distance(t);
+                    win_known = true;
                     const bool on = walk_step_contrib<D, F>(c, it.w, depth, st, acc, rd, t.win, 1.0f, it.R_B);
                     acc.flush();
                     it.T[0] = acc.tot[0], it.T[1] = acc.tot[1], it.T[2] = acc.tot[2];
@@ -482,6 +484,7 @@ namespace wost
                             depth = a.depth;
                             has = true;
                             rd = c.neu.nprims == 0 ? it.R_B : dm_inf(); // R_B = max(1e-4, R_D) when there is no Neumann mesh
+                            win_known = false;
                         }
                         else
                             exhausted = true;
@@ -500,7 +503,10 @@ namespace wost
                         ++depth;
                         ++my_steps;
                         need_contrib = true;
-                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, (rd + vlen(vsub(it.w.x, x0))) * 1.00001f);
+                        // bound: distance to the primitive that was closest a step ago when this lane knows it, else R_D + |step|
+                        const float bound = (win_known && t.win != kInvalid) ? prim_distance(load_prim(c.dir.leaf_prim + t.win), it.w.x) * 1.00001f
+                                                                             : (rd + vlen(vsub(it.w.x, x0))) * 1.00001f;
+                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, bound);
                     }
                     else
                     {
@@ -1323,6 +1329,8 @@ namespace wost
     template <int D>
     static wost_status solve_guided_impl(wost_integrator *it, uint64_t *walk_steps)
     {
+        if (it->problem->neumann != nullptr && !it->problem->neumann_flux_enabled && it->problem->d_source.ptr == nullptr)
+            return solve_guided_f<D, kFeatNeumann>(it, walk_steps); // data/ladybug, data/fille: reflecting boundary, no source
         if (it->problem->neumann != nullptr)
             return solve_guided_f<D, kFeatAll>(it, walk_steps);
         if (it->problem->d_source.ptr != nullptr)

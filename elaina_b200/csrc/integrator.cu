@@ -213,7 +213,12 @@ namespace wost
                     ++depth;
                     if (!alive || depth >= (uint32_t)a.max_depth)
                         has_walk = false;
-                    bound = (R_D + vlen(vsub(w.x, x0))) * 1.00001f; // triangle inequality, rounding slack on top
+                    // upper bound of the next closest-point distance: the distance from the new point to the primitive that
+                    // was closest a step ago (<= R_D + |step| by the triangle inequality, usually much tighter), rounding slack on top
+                    if (alive && t.win != kInvalid)
+                        bound = prim_distance(load_prim(c.dir.leaf_prim + t.win), w.x) * 1.00001f;
+                    else
+                        bound = (R_D + vlen(vsub(w.x, x0))) * 1.00001f;
                 }
                 const bool want = !has_walk && !exhausted;
                 const unsigned want_mask = __ballot_sync(kFullMask, want);
@@ -471,7 +476,9 @@ namespace wost
     {
         if (RefOrder)
             return solve_persistent_f<D, RefOrder, kFeatAll>(it, walk_steps);
-        const bool neu = it->problem->neumann != nullptr, src = it->problem->d_source.ptr != nullptr;
+        const bool neu = it->problem->neumann != nullptr, src = it->problem->d_source.ptr != nullptr, flux = neu && it->problem->neumann_flux_enabled;
+        if (neu && !flux && !src) // data/ladybug, data/fille: reflecting boundary, no source
+            return solve_persistent_f<D, false, kFeatNeumann>(it, walk_steps);
         if (neu)
             return solve_persistent_f<D, false, kFeatAll>(it, walk_steps);
         if (src)

@@ -307,7 +307,7 @@ namespace wost
     // Problem features a kernel instantiation is compiled for: the host picks the leanest variant the problem allows
     // (no Neumann mesh -> no silhouette query, no ray casts, no hemisphere sampling; no source grid -> no Green's-function
     // sample), which cuts registers and the instruction footprint of the walk kernels.
-    constexpr int kFeatNeumann = 1, kFeatSource = 2, kFeatAll = 3;
+    constexpr int kFeatNeumann = 1, kFeatSource = 2, kFeatFlux = 4 /* non-zero Neumann data: boundary-sample stage */, kFeatAll = 7;
 
     // ---------------------------------------------------------------------------------------------------------
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
@@ -405,7 +405,7 @@ namespace wost
 
         // ---- Neumann boundary sample (integrator.cu:318-445). Skipped when every Neumann colour is zero:
         // the stage could then only add -0 to the pixel ("pure overhead there").
-        if (has_neu && c.neumann_flux_enabled)
+        if ((F & kFeatFlux) && has_neu && c.neumann_flux_enabled)
         {
             const Philox4 q = wost_rng(c.seed, w.pixel, w.sample, depth, WOST_RNG_NEUMANN, 0);
             const float u0 = u32_to_unit_float(q.x), u1 = u32_to_unit_float(q.y), u2 = u32_to_unit_float(q.z);
