@@ -26,6 +26,7 @@
 #include "../../include/wost.h"
 #include "imageio.h"
 #include "json.h"
+#include "nvdb.h"
 
 namespace wost
 {
@@ -291,9 +292,23 @@ namespace
         d.source_intensity = (float)scene.number_or("source_intensity", 1.0);
         d.dirichlet_intensity = (float)scene.number_or("dirichlet_intensity", 1.0);
         d.neumann_intensity = (float)scene.number_or("neumann_intensity", 1.0);
-        if (opt(scene, "source_path"))
-            fail(WOST_ERR_UNSUPPORTED, "source_path (NanoVDB) is not read by this build: pass a dense grid through scene/source_dense");
-        if (const wjson::Value *sd = opt(scene, "source_dense"))
+        if (const wjson::Value *sp = opt(scene, "source_path"))
+        {
+            // core/problem.cu:135-149: a NanoVDB Vec3f grid, flattened over its index bounding box (nvdb.h)
+            wnvdb::DenseVec3f g;
+            const std::string err = wnvdb::read_vec3f(sp->as_string(), g);
+            if (!err.empty())
+                fail(err.rfind("cannot", 0) == 0 ? WOST_ERR_IO : WOST_ERR_UNSUPPORTED, err);
+            for (int k = 0; k < 3; ++k)
+            {
+                d.source_dims[k] = g.dims[k];
+                d.source_origin[k] = g.origin[k];
+            }
+            d.source_voxel = g.voxel;
+            source.swap(g.data);
+            d.source = source.data();
+        }
+        else if (const wjson::Value *sd = opt(scene, "source_dense"))
         {
             float dims[3];
             get_vec(*sd, "dims", 3, dims);
@@ -481,6 +496,38 @@ namespace
         f << dumped << std::endl;
     }
 } // namespace
+
+extern "C" wost_status wost_nvdb_read_vec3f(const char *path, int dims[3], float origin[3], float *voxel, float *dense, uint64_t capacity_floats)
+{
+    if (!path || !dims || !origin || !voxel)
+    {
+        wost::set_last_error("wost_nvdb_read_vec3f: null argument");
+        return WOST_ERR_INVALID;
+    }
+    wnvdb::DenseVec3f g;
+    const std::string err = wnvdb::read_vec3f(path, g);
+    if (!err.empty())
+    {
+        wost::set_last_error(err);
+        return err.rfind("cannot", 0) == 0 ? WOST_ERR_IO : WOST_ERR_UNSUPPORTED;
+    }
+    for (int k = 0; k < 3; ++k)
+    {
+        dims[k] = g.dims[k];
+        origin[k] = g.origin[k];
+    }
+    *voxel = g.voxel;
+    if (dense)
+    {
+        if (capacity_floats < g.data.size())
+        {
+            wost::set_last_error("wost_nvdb_read_vec3f: buffer too small");
+            return WOST_ERR_INVALID;
+        }
+        memcpy(dense, g.data.data(), g.data.size() * sizeof(float));
+    }
+    return WOST_OK;
+}
 
 extern "C" wost_status wost_run_config(const char *json_path)
 {

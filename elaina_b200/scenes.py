@@ -64,6 +64,19 @@ def save_vertex_colors(path, colors):
         json.dump({"ColorConfigurations": items}, f)
 
 
+def load_nvdb_source(path):
+    """core/problem.cu:135-149 (nanovdb::io::readGrid): -> (dense[nz, ny, nx, 3] float32, origin (x, y, z), voxel size) of the
+    first Vec3f grid of an uncompressed .nvdb file, flattened over its index bounding box by libwost (csrc/nvdb.h)."""
+    import ctypes
+    from . import _lib
+    L = _lib.load()
+    dims, origin, voxel = (ctypes.c_int * 3)(), (ctypes.c_float * 3)(), ctypes.c_float()
+    _lib.check(L.wost_nvdb_read_vec3f(str(path).encode(), dims, origin, ctypes.byref(voxel), None, 0))
+    out = np.zeros((dims[2], dims[1], dims[0], 3), np.float32)
+    _lib.check(L.wost_nvdb_read_vec3f(str(path).encode(), dims, origin, ctypes.byref(voxel), out.ctypes.data, out.size))
+    return out, (origin[0], origin[1], origin[2]), voxel.value
+
+
 def synth_stroke_colors(nverts, prims, seed=7):
     """Deterministic stand-in for the missing data/*/color.json (.MISSING_LARGE_BLOBS): piecewise-constant
     left/right colour pairs per connected stroke of the polyline soup (diffusion-curve style)."""

@@ -205,6 +205,13 @@ extern "C"
     typedef int (*wost_allreduce_fn)(void *user, void *d_buf, uint64_t n_floats, void *stream);
     wost_status wost_set_allreduce(wost_integrator *it, wost_allreduce_fn fn, void *user);
 
+    /* NanoVDB source grids (core/problem.cu:135-149 reads them with nanovdb::io::readGrid; the walker samples them with
+     * worldToIndex + SampleFromVoxels<Vec3fTree, 1, false>, integrator/uniform/integrator.cu:309-311). Host-side: flattens
+     * the first grid of an uncompressed .nvdb file (Vec3f, axis-aligned uniform map, zero background) over its index
+     * bounding box into the dense grid wost_problem_desc takes. Call with dense == NULL to get dims / origin / voxel, then
+     * with a buffer of dims[0]*dims[1]*dims[2]*3 floats ([z][y][x][rgb]). */
+    wost_status wost_nvdb_read_vec3f(const char *path, int dims[3], float origin[3], float *voxel, float *dense, uint64_t capacity_floats);
+
     /* Progressive metrics (integrator/uniform/integrator.cu:577-609, "frames/<sampleId>" and "frames_time/<ms>"): when
      * settings.save_spp_metrics_duration > 0 or save_time_metrics_duration > 0, wost_solve() hands the running estimate
      * solution / (sample_id + 1) to this callback after every sample index the reference would dump
