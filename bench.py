@@ -63,12 +63,14 @@ def workload(name):
         # epsilonShell 1, depth 64); the shipped OBJ does not travel to the GPU box and its color.json is missing, so the
         # scene is a seeded stroke soup of the same size (60 strokes x 1024 segments = 61 440 segments)
         dv, dp = scenes.stroke_soup(60, 1024)
-        nv = np.array([[0, 0], [500, 0], [500, 500], [0, 500]], np.float32)
+        # the shipped boundary.obj is a square well outside the evaluation grid (closest distance 190 from (100, 250));
+        # a square ON the grid border would let the border pixels' walks escape into the exterior
+        nv = np.array([[-90, -90], [590, -90], [590, 590], [-90, 590]], np.float32)
         npr = np.array([[0, 1], [1, 2], [2, 3], [3, 0]], np.int32)
         return dict(dim=2, dverts=dv, dprims=dp, nverts=nv, nprims=npr, color_dirichlet=scenes.stroke_colors(60, 1024), color_neumann=None,
                     grid_scale=250.0, grid_pos=(250.0, 250.0), grid_up=(-1.0, 0.0), aabb_min=(-100.0, -100.0), aabb_max=(600.0, 600.0),
                     frame=(1024, 1024), depth=64, spp=256, eps=1.0, seed=42,
-                    desc="synthetic ladybug-shaped 2D mixed problem: 61440-segment Dirichlet stroke soup in a 4-segment Neumann square, 1024x1024 grid, 256 spp, depth 64, epsilonShell 1")
+                    desc="synthetic ladybug-shaped 2D mixed problem: 61440-segment Dirichlet stroke soup in a 4-segment Neumann square [-90,590]^2, 1024x1024 grid, 256 spp, depth 64, epsilonShell 1")
     if name in ("c4", "c4-small"):
         # configs[3]: synthetic 3D Poisson on a displaced icosphere (1,310,720 triangles; c4-small 327,680), one 512x512 slice
         dv, dp = scenes.icosphere(8 if name == "c4" else 7, 1.0, 0.1)

@@ -457,57 +457,57 @@ namespace wost
         return true;
     }
 
+    // distance to one leaf primitive + the bookkeeping of the running minimum (phase 0)
+    template <int D>
+    WOST_DEV void nearest_eval_leaf(const DevBVH<D> &bvh, const Vec<D> &q, NearestTrav<D> &t, uint32_t pos)
+    {
+        const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
+        if (d2 <= t.best * 1.000002f)
+        {
+            const float d = dm_sqrt(d2);
+            const float g = d * d;
+            bool take = g < t.best;
+            if (D == 3)
+            {
+                if (take)
+                    t.n_near = (t.best <= g * 1.000001f) ? t.n_near + 1 : 1;
+                else if (g <= t.best * 1.000001f)
+                    ++t.n_near;
+            }
+            if (take)
+                t.have_rank = false;
+            else if (D == 2 && g == t.best && t.win != kInvalid)
+            {
+                // exact tie: the reference keeps the last visited leaf of its own (static) order
+                const uint32_t rk = __ldg(bvh.leaf_rank + pos);
+                if (!t.have_rank)
+                {
+                    t.best_rank = __ldg(bvh.leaf_rank + t.win);
+                    t.have_rank = true;
+                }
+                take = rk > t.best_rank;
+                if (take)
+                    t.best_rank = rk;
+            }
+            if (take)
+            {
+                t.best = g;
+                t.win = pos;
+                const float u = d + t.slack;
+                t.thr = u * u;
+            }
+        }
+    }
+
     // one trip -> still active
+    // Phase 0 opens ONE internal node per trip and evaluates its leaf children on the spot (nearer one first): leaves never
+    // travel through `cur` or the stack, so a query takes ~30% fewer trips and the stack only ever holds internal nodes.
     template <int D, bool RefOrder>
     WOST_DEV bool nearest_trip(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
     {
         if (RefOrder || t.phase == 1)
             return nearest_trip_ref<D, RefOrder>(bvh, q, st, t);
         bool have = false;
-        if (t.cur & kLeafFlag)
-        {
-            if (t.cur_d <= t.thr)
-            {
-                const uint32_t pos = t.cur & ~kLeafFlag;
-                const float d2 = prim_distance_d2(load_prim(bvh.leaf_prim + pos), q);
-                if (d2 <= t.best * 1.000002f)
-                {
-                    const float d = dm_sqrt(d2);
-                    const float g = d * d;
-                    bool take = g < t.best;
-                    if (D == 3)
-                    {
-                        if (take)
-                            t.n_near = (t.best <= g * 1.000001f) ? t.n_near + 1 : 1;
-                        else if (g <= t.best * 1.000001f)
-                            ++t.n_near;
-                    }
-                    if (take)
-                        t.have_rank = false;
-                    else if (D == 2 && g == t.best && t.win != kInvalid)
-                    {
-                        // exact tie: the reference keeps the last visited leaf of its own (static) order
-                        const uint32_t rk = __ldg(bvh.leaf_rank + pos);
-                        if (!t.have_rank)
-                        {
-                            t.best_rank = __ldg(bvh.leaf_rank + t.win);
-                            t.have_rank = true;
-                        }
-                        take = rk > t.best_rank;
-                        if (take)
-                            t.best_rank = rk;
-                    }
-                    if (take)
-                    {
-                        t.best = g;
-                        t.win = pos;
-                        const float u = d + t.slack;
-                        t.thr = u * u;
-                    }
-                }
-            }
-        }
-        else
         {
             const NodeViewE<D> n = load_tnode_e(bvh.tnodes + t.cur);
             const float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
@@ -519,9 +519,30 @@ namespace wost
                     goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
                 if (goR)
                     goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
+                const bool lnear = Le <= Re;
+                // leaf children: evaluate now, nearer first (the second one only if it can still matter)
+                const bool leafL = goL && (n.lref & kLeafFlag), leafR = goR && (n.rref & kLeafFlag);
+                if (leafL || leafR)
+                {
+                    const bool firstL = leafL && (lnear || !leafR);
+                    const uint32_t p1 = (firstL ? n.lref : n.rref) & ~kLeafFlag;
+                    nearest_eval_leaf<D>(bvh, q, t, p1);
+                    if (leafL && leafR)
+                    {
+                        const float d2nd = firstL ? Re : Le;
+                        if (d2nd <= t.thr)
+                            nearest_eval_leaf<D>(bvh, q, t, (firstL ? n.rref : n.lref) & ~kLeafFlag);
+                    }
+                    if (leafL)
+                        goL = false;
+                    if (leafR)
+                        goR = false;
+                    // the threshold may have shrunk: re-test the internal sibling
+                    goL = goL && Le <= t.thr;
+                    goR = goR && Re <= t.thr;
+                }
                 if (goL && goR)
                 {
-                    const bool lnear = Le <= Re;
                     st.push(lnear ? n.rref : n.lref, lnear ? Re : Le);
                     t.cur = lnear ? n.lref : n.rref;
                     t.cur_d = lnear ? Le : Re;
