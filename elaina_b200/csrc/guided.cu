@@ -1280,9 +1280,21 @@ namespace wost
         GuideNet &n = *it->net;
         GuidedBuffers &g = it->gb;
         cudaStream_t st = it->stream;
-        const int bs = it->s.train_batch_size > 0 ? it->s.train_batch_size : 524288;
-        const int minb = it->s.train_min_batch > 0 ? it->s.train_min_batch : 65536;
+        int bs = it->s.train_batch_size > 0 ? it->s.train_batch_size : 524288;
+        int minb = it->s.train_min_batch > 0 ? it->s.train_min_batch : 65536;
         const int per_frame = std::min(8, it->s.train_batches_per_frame > 0 ? it->s.train_batches_per_frame : 5);
+        // data-parallel training (gradient all-reduce installed): one optimiser step consumes the UNION of the ranks' batches,
+        // so every rank takes 1/num_shards of the global batch -- the same number of optimiser steps per frame and the same
+        // global batch size as a single-GPU run. The step count must be identical on all ranks (collectives): it is sized from
+        // the frame-wide active-pixel count, which every rank knows.
+        const int shards = (it->allreduce && it->s.num_shards > 1) ? it->s.num_shards : 1;
+        const long long cap_frame = (long long)kMaxTrainDepth * std::max(1, it->allreduce ? it->n_active_frame : it->n_active);
+        const int max_frame_batches = (int)std::min<long long>(per_frame, cap_frame / bs + 1);
+        if (shards > 1)
+        {
+            bs = std::max(128, bs / shards / 128 * 128);
+            minb = std::max(128, minb / shards / 128 * 128);
+        }
         int *opt_steps = &n.ctl.ptr->opt_steps[0];
         k_g_frame_ctl<<<1, 1, 0, st>>>(n.ctl.ptr, opt_steps, 0);
         k_g_count_samples<D><<<div_up(it->n_active + 1, 256), 256, 0, st>>>(ctx, it->d_active.ptr, it->n_active, it->npix, g.rec.ptr, g.rec_onN.ptr,
@@ -1293,7 +1305,7 @@ namespace wost
                                                                              g.rec_count.ptr, g.total.ptr, g.sample_off.ptr, g.cap, g.smp.ptr, g.smp_onN.ptr, n.ctl.ptr);
         it->launches += 4;
         // with a gradient all-reduce every rank must issue the same number of collectives, whatever its own sample count
-        const int max_batches = it->allreduce ? per_frame : std::min(per_frame, g.cap / bs + 1);
+        const int max_batches = it->allreduce ? max_frame_batches : std::min(per_frame, g.cap / bs + 1);
         for (int iter = 0; iter < max_batches; ++iter)
         {
             WOST_CUDA_TRY(cudaMemsetAsync(n.grad.ptr, 0, sizeof(float) * ((size_t)n.n_params + 4), st));

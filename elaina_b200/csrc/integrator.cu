@@ -724,6 +724,7 @@ extern "C"
         {
             if (mask && !mask[p])
                 continue;
+            ++it->n_active_frame;
             if (s.pixel_stride_rows > 0 && s.num_shards > 1)
             {
                 const int row = p / s.frame_w;

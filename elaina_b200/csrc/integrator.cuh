@@ -28,6 +28,7 @@ struct wost_integrator
     int kind = 0, dim = 0, device = 0;
     int npix = 0;
     int n_active = 0;  // pixels of this shard that pass the mask
+    int n_active_frame = 0; // the same count over ALL shards (identical on every rank: sizes the training batches)
     int spp_batch = 1; // S: samples of every pixel in flight per wavefront
     size_t queue_capacity = 0;
     wost::DevBuf<uint32_t> d_active;
