@@ -36,18 +36,19 @@ METRIC = "walk_steps_per_sec"
 UNIT = "walk-steps/s"
 
 # algorithmic bytes per walk-step (DESIGN.md "Roofline"): state in/out + one root->leaf descent per query
-BYTES_PER_STEP = {"c3": 938, "c3-small": 938, "c4": 1734, "c4-small": 1734, "c1": 1850}  # c4: 1910 with guiding I/O (added below)
+BYTES_PER_STEP = {"c3": 938, "c3-small": 938, "c5": 938, "c4": 1734, "c4-small": 1734, "c1": 1850}  # c4: 1910 with guiding I/O (added below)
 
 
 def workload(name):
     """-> dict(spec for Problem, settings kwargs, description). Synthetic scenes of BASELINE.json's named shapes."""
     from elaina_b200 import scenes
-    if name in ("c3", "c3-small"):
+    if name in ("c3", "c3-small", "c5"):
         # configs[2]: synthetic 2D Laplace, 10k-segment polygon, analytic harmonic solution Re(z^3), 1024^2, 256 spp
         nseg = 10000
         dv, dp = scenes.star_polygon(nseg)
-        W = 1024 if name == "c3" else 256
-        spp = 256 if name == "c3" else 16
+        # c5 = configs[4]: the strong-scaling frame (4096^2, 1024 spp) on the same geometry
+        W = {"c3": 1024, "c3-small": 256, "c5": 4096}[name]
+        spp = {"c3": 256, "c3-small": 16, "c5": 1024}[name]
         diag = float(np.linalg.norm(np.array([3.0, 3.0])))
         # evaluate the interior problem only (that is where Re(z^3) is the solution): mask = pixels inside the curve
         g = 1.5 * (2.0 * np.arange(W, dtype=np.float64) / W - 1.0)
@@ -358,7 +359,7 @@ def main():
     peak, peak_src = measured_peak()
     bps = BYTES_PER_STEP[args.workload] + (176 if guided else 0)  # + 12 B network input and 164 B output per guided step
     relmse = None
-    if rank == 0 and world == 1 and args.workload.startswith("c3"):
+    if rank == 0 and world == 1 and args.workload in ("c3", "c3-small"):
         # relMSE against the analytic field Re(z^3) over the evaluated pixels (BASELINE metric, second half)
         from elaina_b200 import scenes as _sc
         g = 1.5 * (2.0 * np.arange(W, dtype=np.float64) / W - 1.0)
