@@ -514,11 +514,28 @@ namespace wost
             bool goL = Le <= t.thr, goR = Re <= t.thr;
             if (goL || goR)
             {
+                // the reference's sibling rule on the padded boxes: child X is visited iff mindist(X) <= minmaxdist(Y).
+                // mindist(B) <= minmaxdist(B) holds for every box also in fp32 (same subtractions, same summation order,
+                // termwise <=, monotone rounding), so the child whose padded mindist does not exceed its sibling's passes
+                // without evaluating the rule: at most ONE minmaxdist per node, that of the nearer child's box.
                 const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
-                if (goL)
-                    goL = box_mindist(lp, q) <= box_minmaxdist(rp, q);
-                if (goR)
-                    goR = box_mindist(rp, q) <= box_minmaxdist(lp, q);
+                const float Lp = box_mindist(lp, q), Rp = box_mindist(rp, q);
+                const bool testL = goL && Lp > Rp, testR = goR && Rp > Lp;
+                if (testL || testR)
+                {
+                    Box<D> nb;
+#pragma unroll
+                    for (int k = 0; k < D; ++k)
+                    {
+                        nb.up[k] = testL ? rp.up[k] : lp.up[k];
+                        nb.lo[k] = testL ? rp.lo[k] : lp.lo[k];
+                    }
+                    const float mm = box_minmaxdist(nb, q);
+                    if (testL)
+                        goL = Lp <= mm;
+                    else
+                        goR = Rp <= mm;
+                }
                 const bool lnear = Le <= Re;
                 // leaf children: evaluate now, nearer first (the second one only if it can still matter)
                 const bool leafL = goL && (n.lref & kLeafFlag), leafR = goR && (n.rref & kLeafFlag);
