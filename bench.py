@@ -372,7 +372,7 @@ def main():
 
     traffic = None
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic_r1c.json")))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic_r1d.json")))
         if not guided and tj.get("kernel", "").split("<")[0] in ("k_walk_persistent" if args.walk_mode.startswith("persistent") else "k_step_uniform") and dim == 2:
             traffic = tj["dram_bytes_per_walk_step"] * steps_total / max(1, kern_launches)  # DRAM bytes per launch, from the committed ncu capture
     except Exception:

@@ -3,6 +3,9 @@
 // One walk = one (pixel, sample); the per-depth stage order of the reference
 // (separate -> boundary -> source -> neumann -> walk, integrator.cu:552-575) is kept inside the loop.
 // RNG: Philox stream of elaina_b200/csrc/philox.h instead of the per-pixel PCG32 (core/sampler.h).
+// PARITY UNPINNED for this layer (uniform walker): the reference ships no golden fields and its integrators cannot run without a GPU
+// build. What IS pinned: the LBVH layer underneath (bit-exact against the host-compiled reference headers,
+// oracle/_ref) and the special functions (known answers of test/vonmises_test.cu); fields are checked against analytic solutions.
 
 namespace
 {
