@@ -505,7 +505,7 @@ namespace wost
     template <int D, bool RefOrder>
     WOST_DEV bool nearest_trip(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
     {
-        if (RefOrder || t.phase == 1)
+        if (RefOrder || __builtin_expect(t.phase == 1, 0)) // phase 1: far field / 3D tie resolution, kept off the hot path
             return nearest_trip_ref<D, RefOrder>(bvh, q, st, t);
         bool have = false;
         {
@@ -585,7 +585,7 @@ namespace wost
                 return true;
             }
         }
-        if (D == 3 && t.n_near > 1)
+        if (D == 3 && __builtin_expect(t.n_near > 1, 0))
         {
             nearest_enter_phase1(bvh, q, st, t, t.thr);
             return true;
