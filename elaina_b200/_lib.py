@@ -116,6 +116,7 @@ SYMBOLS = [
     ("wost_vmm_eval", c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_u32, c_void_p, c_void_p, c_void_p]),
     ("wost_set_allreduce", c_int, [c_void_p, c_void_p, c_void_p]),
     ("wost_set_frame_callback", c_int, [c_void_p, c_void_p, c_void_p]),
+    ("wost_trim_allocation_cache", c_int, []),
     ("wost_nvdb_read_vec3f", c_int, [ctypes.c_char_p, c_void_p, c_void_p, c_void_p, c_void_p, c_u64]),
     ("wost_guided_last_profile", c_int, [c_void_p, c_void_p]),
     ("wost_guided_last_stats", c_int, [c_void_p, _PP(c_u64), _PP(c_u64), _PP(c_float)]),

@@ -10,6 +10,12 @@
 namespace wost
 {
     void set_last_error(const std::string &msg);
+    // Device allocations of libwost.so. Blocks >= 1 MiB are not returned to the driver when released but parked in a
+    // per-device free list keyed by exact size (scene.cu): re-creating a scene / problem / integrator of the same shape --
+    // what a host does between solves -- then costs neither cudaMalloc nor cudaFree (the latter took up to 60 ms for the
+    // accumulator and queue buffers). wost_trim_allocation_cache() hands everything back.
+    cudaError_t dev_alloc(void **ptr, size_t bytes);
+    void dev_free(void *ptr, size_t bytes);
 
     struct CudaError
     {
@@ -43,7 +49,7 @@ namespace wost
         void release()
         {
             if (ptr)
-                cudaFree(ptr);
+                dev_free(ptr, count * sizeof(T));
             ptr = nullptr;
             count = 0;
         }
@@ -53,7 +59,7 @@ namespace wost
             count = n;
             if (n == 0)
                 return cudaSuccess;
-            return cudaMalloc(&ptr, n * sizeof(T));
+            return dev_alloc(reinterpret_cast<void **>(&ptr), n * sizeof(T));
         }
         cudaError_t upload(const T *host, size_t n, cudaStream_t s = 0)
         {

@@ -24,6 +24,78 @@ namespace wost
     static thread_local std::string g_last_error;
     void set_last_error(const std::string &msg) { g_last_error = msg; }
     const std::string &last_error() { return g_last_error; }
+    // ------------------------------------------------------------------ caching device allocator (common.cuh)
+    namespace
+    {
+        struct AllocCache
+        {
+            std::mutex mu;
+            std::unordered_multimap<unsigned long long, void *> free_blocks; // key = device << 48 | bytes
+            size_t cached_bytes = 0;
+        };
+        AllocCache &alloc_cache()
+        {
+            static AllocCache c;
+            return c;
+        }
+        constexpr size_t kCacheMinBytes = (size_t)1 << 20, kCacheMaxBytes = (size_t)16 << 30;
+        bool alloc_cache_enabled()
+        {
+            static const bool on = getenv("WOST_NO_ALLOC_CACHE") == nullptr;
+            return on;
+        }
+        unsigned long long cache_key(size_t bytes)
+        {
+            int dev = 0;
+            cudaGetDevice(&dev);
+            return ((unsigned long long)dev << 48) | (unsigned long long)bytes;
+        }
+    } // namespace
+    cudaError_t dev_alloc(void **ptr, size_t bytes)
+    {
+        if (bytes >= kCacheMinBytes && alloc_cache_enabled())
+        {
+            AllocCache &c = alloc_cache();
+            std::lock_guard<std::mutex> lock(c.mu);
+            auto it = c.free_blocks.find(cache_key(bytes));
+            if (it != c.free_blocks.end())
+            {
+                *ptr = it->second;
+                c.free_blocks.erase(it);
+                c.cached_bytes -= bytes;
+                return cudaSuccess;
+            }
+        }
+        cudaError_t e = cudaMalloc(ptr, bytes);
+        if (e != cudaSuccess && bytes >= kCacheMinBytes)
+        {
+            // out of memory with blocks parked in the cache: give them back and retry once
+            cudaGetLastError();
+            wost_trim_allocation_cache();
+            e = cudaMalloc(ptr, bytes);
+        }
+        return e;
+    }
+    void dev_free(void *ptr, size_t bytes)
+    {
+        if (!ptr)
+            return;
+        if (bytes >= kCacheMinBytes && alloc_cache_enabled())
+        {
+            AllocCache &c = alloc_cache();
+            std::lock_guard<std::mutex> lock(c.mu);
+            if (c.cached_bytes + bytes <= kCacheMaxBytes)
+            {
+                // a parked block may be handed out again at once: no work of any stream may still touch it (cudaFree waits too)
+                cudaDeviceSynchronize();
+                c.free_blocks.emplace(cache_key(bytes), ptr);
+                c.cached_bytes += bytes;
+                return;
+            }
+        }
+        cudaFree(ptr);
+    }
+
     int sm_count()
     {
         int dev = 0, n = 148;
@@ -1101,6 +1173,22 @@ extern "C"
         if (cudaGetDeviceCount(&n) != cudaSuccess)
             return 0;
         return n;
+    }
+    wost_status wost_trim_allocation_cache(void)
+    {
+        AllocCache &c = alloc_cache();
+        std::lock_guard<std::mutex> lock(c.mu);
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (auto &kv : c.free_blocks)
+        {
+            cudaSetDevice((int)(kv.first >> 48));
+            cudaFree(kv.second);
+        }
+        cudaSetDevice(cur);
+        c.free_blocks.clear();
+        c.cached_bytes = 0;
+        return WOST_OK;
     }
     wost_status wost_set_device(int device)
     {

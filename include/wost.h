@@ -30,6 +30,10 @@ extern "C"
     const char *wost_version(void);
     /* replaces Context::initialize (core/device/context.cpp:12-39, device 0 hard-coded there) */
     wost_status wost_set_device(int device);
+    /* libwost.so parks released device blocks >= 1 MiB in a per-device free list (the reference never frees anything,
+     * integrator/uniform/integrator.cu:25-60; here handles can be destroyed and re-created at no allocation cost).
+     * This call returns every parked block to the driver. WOST_NO_ALLOC_CACHE=1 in the environment disables the cache. */
+    wost_status wost_trim_allocation_cache(void);
     int wost_device_count(void);
 
     /* ------------------------------------------------------------------ geometry: one mesh + its SNCH-LBVH
