@@ -176,8 +176,11 @@ namespace wost
         int *overflow;
     };
 
+    // resident CTAs per SM the lean 3D variants are compiled for (64 registers: a few spilled bytes buy an eighth CTA; c4 +8%);
+    // 0 = no request, the compiler's own budget (an explicit request cost the 2D kernels 2-7%)
+    constexpr int persist_min_ctas(int D, bool ref_order, int F) { return (D == 3 && !ref_order && !(F & kFeatNeumann)) ? 8 : 0; }
     template <int D, bool RefOrder, int F>
-    __global__ void __launch_bounds__(kWalkBlock) k_walk_persistent(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ PersistArgs a)
+    __global__ void __launch_bounds__(kWalkBlock, persist_min_ctas(D, RefOrder, F)) k_walk_persistent(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ PersistArgs a)
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
