@@ -185,8 +185,10 @@ namespace wost
     // (profiles/r1_notes.md), refilling keeps the traversal -- the bulk of the instructions -- near full width.
     // First: items are synthesised from (pixel, sample) = generateEvaluationPointsImpl (integrator.cu:131-151).
     constexpr int kGRefill = 6;
+    // lean 3D variants are compiled for 8 CTAs/SM like k_walk_persistent (integrator.cu: persist_min_ctas); 0 = compiler's budget
+    constexpr int g_min_ctas(int D, int F) { return (D == 3 && !(F & kFeatNeumann)) ? 8 : 0; }
     template <int D, bool First, int F>
-    __global__ void __launch_bounds__(kGBlock) k_g_arrive(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
+    __global__ void __launch_bounds__(kGBlock, g_min_ctas(D, F)) k_g_arrive(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
@@ -422,7 +424,7 @@ namespace wost
     // stages of the point just reached, then uniform direction + walk record + move; lanes without a walk claim the
     // next out-shell item of the queue.
     template <int D, int F>
-    __global__ void __launch_bounds__(kGBlock) k_g_finish(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
+    __global__ void __launch_bounds__(kGBlock, g_min_ctas(D, F)) k_g_finish(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a)
     {
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
