@@ -35,65 +35,7 @@ import numpy as np
 METRIC = "walk_steps_per_sec"
 UNIT = "walk-steps/s"
 
-# algorithmic bytes per walk-step (DESIGN.md "Roofline"): state in/out + one root->leaf descent per query
-BYTES_PER_STEP = {"c3": 938, "c3-small": 938, "c5": 938, "c4": 1734, "c4-small": 1734, "c1": 1850}  # c4: 1910 with guiding I/O (added below)
-
-
-def workload(name):
-    """-> dict(spec for Problem, settings kwargs, description). Synthetic scenes of BASELINE.json's named shapes."""
-    from elaina_b200 import scenes
-    if name in ("c3", "c3-small", "c5"):
-        # configs[2]: synthetic 2D Laplace, 10k-segment polygon, analytic harmonic solution Re(z^3), 1024^2, 256 spp
-        nseg = 10000
-        dv, dp = scenes.star_polygon(nseg)
-        # c5 = configs[4]: the strong-scaling frame (4096^2, 1024 spp) on the same geometry
-        W = {"c3": 1024, "c3-small": 256, "c5": 4096}[name]
-        spp = {"c3": 256, "c3-small": 16, "c5": 1024}[name]
-        diag = float(np.linalg.norm(np.array([3.0, 3.0])))
-        # evaluate the interior problem only (that is where Re(z^3) is the solution): mask = pixels inside the curve
-        g = 1.5 * (2.0 * np.arange(W, dtype=np.float64) / W - 1.0)
-        X, Y = np.meshgrid(g, g)
-        mask = (np.hypot(X, Y) < 1.0 + 0.3 * np.sin(5.0 * np.arctan2(Y, X)) - 4e-3).astype(np.uint8)
-        return dict(dim=2, dverts=dv, dprims=dp, nverts=None, nprims=None, mask=mask,
-                    color_dirichlet=scenes.gray_pairs(scenes.harmonic_2d(dv, 3)), color_neumann=None,
-                    grid_scale=1.5, grid_pos=(0.0, 0.0), grid_up=(0.0, 1.0), aabb_min=(-1.5, -1.5), aabb_max=(1.5, 1.5),
-                    frame=(W, W), depth=64, spp=spp, eps=1e-3 * diag, seed=42,
-                    desc="synthetic 2D Laplace, %d-segment star polygon, g=Re(z^3), %dx%d grid masked to the interior (%d active pixels), %d spp, depth 64" % (nseg, W, W, int(mask.sum()), spp))
-    if name == "c1":
-        # configs[0] shape (data/ladybug: 61 476 open strokes + 4-segment Neumann square, AABB [-100,600]^2, grid [0,500]^2,
-        # epsilonShell 1, depth 64); the shipped OBJ does not travel to the GPU box and its color.json is missing, so the
-        # scene is a seeded stroke soup of the same size (60 strokes x 1024 segments = 61 440 segments)
-        dv, dp = scenes.stroke_soup(60, 1024)
-        # the shipped boundary.obj is a square well outside the evaluation grid (closest distance 190 from (100, 250), SURVEY 8(c));
-        # a square ON the grid border would let the border pixels' walks escape into the exterior
-        nv = np.array([[-90, -90], [590, -90], [590, 590], [-90, 590]], np.float32)
-        npr = np.array([[0, 1], [1, 2], [2, 3], [3, 0]], np.int32)
-        return dict(dim=2, dverts=dv, dprims=dp, nverts=nv, nprims=npr, color_dirichlet=scenes.stroke_colors(60, 1024), color_neumann=None,
-                    grid_scale=250.0, grid_pos=(250.0, 250.0), grid_up=(-1.0, 0.0), aabb_min=(-100.0, -100.0), aabb_max=(600.0, 600.0),
-                    frame=(1024, 1024), depth=64, spp=256, eps=1.0, seed=42,
-                    desc="synthetic ladybug-shaped 2D mixed problem: 61440-segment Dirichlet stroke soup in a 4-segment Neumann square [-90,590]^2, 1024x1024 grid, 256 spp, depth 64, epsilonShell 1")
-    if name in ("c4", "c4-small"):
-        # configs[3]: synthetic 3D Poisson on a displaced icosphere (1,310,720 triangles; c4-small 327,680), one 512x512 slice
-        dv, dp = scenes.icosphere(8 if name == "c4" else 7, 1.0, 0.1)
-        src = np.ones((16, 16, 16, 3), np.float32)
-        # interior problem (like c3): evaluate the pixels of the slice that lie inside the surface (r >= 0.9 everywhere)
-        g = 2.0 * np.arange(512, dtype=np.float64) / 512 - 1.0
-        X, Y = np.meshgrid(g, g)
-        mask = (np.hypot(X, Y) < 0.88).astype(np.uint8)
-        return dict(dim=3, dverts=dv, dprims=dp, nverts=None, nprims=None, mask=mask,
-                    color_dirichlet=scenes.gray_pairs(scenes.harmonic_3d(dv)), color_neumann=None,
-                    source=src, source_origin=(-1.6, -1.6, -1.6), source_voxel=0.2,
-                    grid_scale=1.0, grid_pos=(0.0, 0.0, 0.0), grid_up=(0.0, 1.0, 0.0), grid_right=(1.0, 0.0, 0.0),
-                    aabb_min=(-1.5, -1.5, -1.5), aabb_max=(1.5, 1.5, 1.5),
-                    frame=(512, 512), depth=64, spp=64, eps=2e-3, seed=42,
-                    desc="synthetic 3D Poisson, %d-triangle displaced icosphere, 512x512 slice z=0 masked to the interior (%d active pixels), 64 spp, depth 64" % (len(dp), int(mask.sum())))
-    raise SystemExit("unknown workload " + name)
-
-
-def problem_kwargs(wl):
-    keys = ("color_dirichlet", "color_neumann", "mask", "source", "source_origin", "source_voxel", "grid_scale", "grid_pos", "grid_up",
-            "grid_right", "aabb_min", "aabb_max")
-    return {k: wl[k] for k in keys if wl.get(k) is not None}
+from elaina_b200.workloads import workload, problem_kwargs, guided_settings  # noqa: E402  (BASELINE.json configurations)
 
 
 class ClockSampler(threading.Thread):
@@ -268,10 +210,9 @@ def main():
     gkw = {}
     if guided:
         # data/{ladybug,fille}/n.json: trainSppCount = spp/4, maxGuidedDepth 10 in both phases, uniformFraction 0.5 (= learned selection)
-        gkw = dict(train_spp_count=max(1, wl["spp"] // 4), max_guided_depth_training=10, max_guided_depth_guiding=10,
-                   uniform_fraction_training=0.5, uniform_fraction_guiding=0.5, mlp_impl=args.mlp_impl)
+        gkw = dict(guided_settings(wl), mlp_impl=args.mlp_impl)
     settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=args.spp_batch, walk_mode={"persistent": 1, "reforder": 2, "wavefront": 3, "persistent-reforder": 4}[args.walk_mode], **shard, **gkw)
-    Integrator = (lambda p, st: api.GuidedIntegrator(p, st, api.DEFAULT_NETWORK)) if guided else api.UniformIntegrator
+    Integrator = (lambda p, st: api.GuidedIntegrator(p, st, wl["network"])) if guided else api.UniformIntegrator
 
     def make_problem():
         g_d = api.Scene(dim, wl["dverts"], wl["dprims"])
@@ -357,7 +298,7 @@ def main():
         e2e_value = sum_over_ranks(float(e2e_steps)) / e2e_t
 
     peak, peak_src = measured_peak()
-    bps = BYTES_PER_STEP[args.workload] + (176 if guided else 0)  # + 12 B network input and 164 B output per guided step
+    bps = wl["bytes_per_step"] + (176 if guided else 0)  # + 12 B network input and 164 B output per guided step
     relmse = None
     if rank == 0 and world == 1 and args.workload in ("c3", "c3-small"):
         # relMSE against the analytic field Re(z^3) over the evaluated pixels (BASELINE metric, second half)

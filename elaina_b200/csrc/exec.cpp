@@ -10,6 +10,7 @@
 //   * source term: "source_dense": {"path": raw float32 file, "dims": [nx,ny,nz], "origin": [x,y,z], "voxel": h} -- a
 //     dense Vec3f grid; NanoVDB files (source_path) are SURVEY 8(f) row N3 and return WOST_ERR_UNSUPPORTED;
 //   * integrator.setting may carry "seed", "sppBatch"; result.json also reports walk_steps and walk_steps_per_sec;
+//   * export type "raw" writes <file_name>.f32, the fp32 film {r,g,b,a,weight} x W*H unflipped (the .exr/.png pair is for viewing);
 //   * errors come back as wost_status (reference: exit(1) / uncaught std::runtime_error).
 #include <sys/stat.h>
 
@@ -471,6 +472,15 @@ namespace
                     tone(tname, lum[p], (lum[p] - lo) / (hi - lo), &rgba[p * 4]);
                     rgba[p * 4 + 3] = 1.0f;
                 }
+            }
+            else if (etype == "raw")
+            {
+                // extension (the reference skips export types it does not know): the fp32 film {r,g,b,a,weight} x W*H, unflipped
+                std::ofstream rf(out_dir + "/" + file_name + ".f32", std::ios::binary);
+                rf.write(reinterpret_cast<const char *>(film.data()), (std::streamsize)(film.size() * sizeof(float)));
+                if (!rf)
+                    fail(WOST_ERR_IO, "cannot write " + out_dir + "/" + file_name + ".f32");
+                continue;
             }
             else
                 continue;

@@ -20,6 +20,8 @@ namespace
     // ------------------------------------------------------------------ math mode
     // mode 0: detmath (== CUDA product arithmetic); mode 1: libm (== host-compiled reference)
     int g_math_mode = 0;
+    // uniform walker draws: 0 = Philox (product), 1 = the reference's per-pixel PCG32 (wost_oracle_walk.inl)
+    int g_rng_mode = 0;
     inline float m_acos(float x) { return g_math_mode ? acosf(x) : dm_acos(x); }
     inline float m_asin(float x) { return g_math_mode ? asinf(x) : dm_asin(x); }
     inline float m_atan2(float y, float x) { return g_math_mode ? atan2f(y, x) : dm_atan2(y, x); }
@@ -1383,6 +1385,7 @@ namespace
 extern "C"
 {
     void orc_set_math_mode(int mode) { g_math_mode = mode; }
+    void orc_set_rng_mode(int mode) { g_rng_mode = mode; }
 
     void *orc_scene_create(int dim, const float *verts, int nverts, const int *idx, int nprims)
     {

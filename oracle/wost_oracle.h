@@ -22,6 +22,10 @@ extern "C"
 #endif
 
     void orc_set_math_mode(int mode); /* 0 = detmath (default), 1 = libm (matches oracle/_ref) */
+    /* uniform walker draws: 0 = Philox stream of the product (default); 1 = the reference's per-pixel PCG32 in its
+     * consumption order (core/sampler.h:10-103, integrator/uniform/integrator.cu:72-77), to compare orc_solve_uniform
+     * field-for-field with the reference's own CUDA build (tests/golden/b1_*.npz) */
+    void orc_set_rng_mode(int mode);
 
     /* ---- geometry ---- */
     void *orc_scene_create(int dim, const float *verts, int nverts, const int *idx, int nprims);

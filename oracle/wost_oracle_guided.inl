@@ -622,7 +622,16 @@ namespace
                 if (rr.hit)
                     dist = dm_fmin(rr.t, dist);
             }
-            const float r = green_sample_radius(R_B, S.seed, pixel, sample, depth, q, (Vec<D> *)nullptr);
+            Draws dr; // Philox stream only (the guided walker has no PCG mode): 2D restarts a block per iteration, 3D continues with words z, w of q
+            dr.mode = 0;
+            dr.seed = S.seed;
+            dr.pixel = pixel;
+            dr.sample = sample;
+            dr.depth = depth;
+            dr.pcg = nullptr;
+            dr.q = q;
+            dr.k = 2;
+            const float r = green_sample_radius(R_B, dr, (Vec<D> *)nullptr);
             if (r <= dist)
             {
                 float w3[3] = {x[0] + r * dir[0], x[1] + r * dir[1], 0.0f};

@@ -2,7 +2,9 @@
 // WoSt integrator (integrator/uniform/integrator.cu:64-623) on top of the oracle LBVH.
 // One walk = one (pixel, sample); the per-depth stage order of the reference
 // (separate -> boundary -> source -> neumann -> walk, integrator.cu:552-575) is kept inside the loop.
-// RNG: Philox stream of elaina_b200/csrc/philox.h instead of the per-pixel PCG32 (core/sampler.h).
+// RNG: mode 0 (default) = the Philox stream of elaina_b200/csrc/philox.h (what the CUDA product draws, bit for bit);
+// mode 1 = the reference's per-pixel PCG32 (core/sampler.h) in its consumption order, for field-for-field comparison with
+// the reference's own CUDA build (baseline/_ref/elaina-exec-ref, tests/golden/b1_*.npz).
 // PARITY UNPINNED for this layer (uniform walker): the reference ships no golden fields and its integrators cannot run without a GPU
 // build. What IS pinned: the LBVH layer underneath (bit-exact against the host-compiled reference headers,
 // oracle/_ref) and the special functions (known answers of test/vonmises_test.cu); fields are checked against analytic solutions.
@@ -210,17 +212,127 @@ namespace
         static float green_norm(float R) { return R * R / 6.0f; }
     };
 
+    // The reference's per-pixel generator (core/sampler.h:10-103): PCG32 (64-bit LCG, XSH-RR output), seeded by
+    // setPixelSample(pixelCoord, 0) and advanced by 256 * pixelId (integrator/uniform/integrator.cu:72-77), then consumed
+    // in kernel order: sample by sample, depth by depth, source -> Neumann -> walk. Only used in rng mode 1, which exists
+    // so that this oracle can be compared field-for-field with the reference's own CUDA build (baseline/_ref).
+    struct Pcg32
+    {
+        uint64_t state = 0, inc = 1;
+        static constexpr uint64_t MULT = 0x5851f42d4c957f2dULL;
+        uint32_t next_uint()
+        {
+            const uint64_t old = state;
+            state = old * MULT + inc;
+            const uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+            const uint32_t rot = (uint32_t)(old >> 59u);
+            return (xs >> rot) | (xs << ((~rot + 1u) & 31));
+        }
+        void set_seed(uint64_t initstate, uint64_t initseq) // sampler.h:20-27
+        {
+            state = 0u;
+            inc = (initseq << 1u) | 1u;
+            next_uint();
+            state += initstate;
+            next_uint();
+        }
+        void advance(int64_t delta) // sampler.h:47-63
+        {
+            uint64_t cur_mult = MULT, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+            while (delta > 0)
+            {
+                if (delta & 1)
+                {
+                    acc_mult *= cur_mult;
+                    acc_plus = acc_plus * cur_mult + cur_plus;
+                }
+                cur_plus = (cur_mult + 1) * cur_plus;
+                cur_mult *= cur_mult;
+                delta /= 2;
+            }
+            state = acc_mult * state + acc_plus;
+        }
+        float next_float() // sampler.h:93-103
+        {
+            union
+            {
+                uint32_t u;
+                float f;
+            } x;
+            x.u = (next_uint() >> 9) | 0x3f800000u;
+            return x.f - 1.0f;
+        }
+        double next_double() // sampler.h:79-91
+        {
+            union
+            {
+                uint64_t u;
+                double d;
+            } x;
+            x.u = ((uint64_t)next_uint() << 20) | 0x3ff0000000000000ULL;
+            return x.d - 1.0;
+        }
+    };
+    inline uint32_t interleave_32bit(uint32_t vx, uint32_t vy) // util/hash.h:13-28
+    {
+        uint32_t x = vx & 0x0000ffff, y = vy & 0x0000ffff;
+        x = (x | (x << 8)) & 0x00FF00FF;
+        x = (x | (x << 4)) & 0x0F0F0F0F;
+        x = (x | (x << 2)) & 0x33333333;
+        x = (x | (x << 1)) & 0x55555555;
+        y = (y | (y << 8)) & 0x00FF00FF;
+        y = (y | (y << 4)) & 0x0F0F0F0F;
+        y = (y | (y << 2)) & 0x33333333;
+        y = (y | (y << 1)) & 0x55555555;
+        return x | (y << 1);
+    }
+    inline Pcg32 pcg_for_pixel(int pixel, int W) // uniform/integrator.cu:72-77
+    {
+        Pcg32 g;
+        g.set_seed(interleave_32bit((uint32_t)(pixel % W), (uint32_t)(pixel / W)), 0);
+        g.advance((int64_t)(256 * pixel));
+        return g;
+    }
+
+    // Where the walker's uniform numbers come from. Mode 0 (product arithmetic): the counter-based Philox stream of
+    // elaina_b200/csrc/philox.h, one 4-word block per (pixel, sample, depth, purpose, iteration), words consumed in order.
+    // Mode 1 (reference arithmetic): the pixel's PCG32 sequence, consumed in call order; begin() is a no-op.
+    struct Draws
+    {
+        int mode;
+        uint32_t seed, pixel, sample, depth;
+        Pcg32 *pcg;
+        Philox4 q;
+        int k;
+        void begin(uint32_t purpose, uint32_t iter)
+        {
+            if (mode == 0)
+            {
+                q = wost_rng(seed, pixel, sample, depth, purpose, iter);
+                k = 0;
+            }
+        }
+        float next()
+        {
+            if (mode != 0)
+                return pcg->next_float();
+            const uint32_t w = k == 0 ? q.x : (k == 1 ? q.y : (k == 2 ? q.z : q.w));
+            ++k;
+            return u32_to_unit_float(w);
+        }
+    };
+
     // util/green.h:45-74 (2D: bounded rejection loop) and :98-113 (3D: closed form)
-    inline float green_sample_radius(float R, uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t depth, const Philox4 &, Vec<2> *)
+    inline float green_sample_radius(float R, Draws &dr, Vec<2> *)
     {
         const float bound = 1.5f / R;
         float r = 0.0f;
         int iter = 0;
         do
         {
-            const Philox4 q = wost_rng(seed, pixel, sample, depth, WOST_RNG_SOURCE_RAD, (uint32_t)iter);
-            const float u = u32_to_unit_float(q.x);
-            r = u32_to_unit_float(q.y) * R;
+            dr.begin(WOST_RNG_SOURCE_RAD, (uint32_t)iter);
+            const float u = dr.next();
+            r = dr.next() * R;
             const float pdf = Dims<2>::green_eval(R, r) / Dims<2>::green_norm(R);
             const float pdfRadius = pdf / Dims<2>::sphere_pdf();
             ++iter;
@@ -232,9 +344,10 @@ namespace
             r = R / 2.0f;
         return r;
     }
-    inline float green_sample_radius(float R, uint32_t, uint32_t, uint32_t, uint32_t, const Philox4 &dirdraw, Vec<3> *)
+    inline float green_sample_radius(float R, Draws &dr, Vec<3> *) // words z, w of the direction block in Philox mode
     {
-        const float u1 = u32_to_unit_float(dirdraw.z), u2 = u32_to_unit_float(dirdraw.w);
+        const float u1 = dr.next();
+        const float u2 = dr.next();
         const float phi = DM_2PI * u2;
         float r = (1.0f + sqrtf(1.0f - m_cbrt(u1 * u1)) * m_cos(phi)) * R / 2.0f;
         r = dm_max(1e-4f, r);
@@ -284,8 +397,20 @@ namespace
         const orc_problem_desc &p = P.d;
         const float eps = S.epsilon_shell;
         sol[0] = sol[1] = sol[2] = 0.0f;
+        Pcg32 pcg = pcg_for_pixel(pixel, S.frame_w);
+        Draws dr;
+        dr.mode = g_rng_mode;
+        dr.seed = S.seed;
+        dr.pixel = (uint32_t)pixel;
+        dr.pcg = &pcg;
+        auto draw_dir = [&dr](float &u1, float &u2) // uniformSampleSphere/Hemisphere: one draw in 2D, two in 3D (util/sampling.h:18-33,68-85)
+        {
+            u1 = dr.next();
+            u2 = D == 3 ? dr.next() : 0.0f;
+        };
         for (int sample = 0; sample < S.samples_per_pixel; ++sample)
         {
+            dr.sample = (uint32_t)sample;
             Vec<D> x = eval_point<D>(p, S.frame_w, S.frame_h, pixel);
             float thp = 1.0f;
             bool onN = false;
@@ -295,6 +420,7 @@ namespace
             for (int depth = 0; depth < S.max_walking_depth; ++depth)
             {
                 ++steps;
+                dr.depth = (uint32_t)depth;
                 // ---- separate (integrator.cu:102-212)
                 float R_D = INF_F;
                 if (sd)
@@ -325,18 +451,20 @@ namespace
                 // ---- source (integrator.cu:234-316)
                 if (p.source)
                 {
-                    const Philox4 q = wost_rng(S.seed, (uint32_t)pixel, (uint32_t)sample, (uint32_t)depth, WOST_RNG_SOURCE_DIR, 0);
+                    dr.begin(WOST_RNG_SOURCE_DIR, 0);
+                    float du1, du2;
+                    draw_dir(du1, du2);
                     Vec<D> dir;
                     float dirPdf, alpha = 1.0f;
                     if (onN)
                     {
-                        dir = to_world(nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
+                        dir = to_world(nN, sample_hemisphere_local(du1, du2, (Vec<D> *)nullptr));
                         dirPdf = Dims<D>::hemi_pdf();
                         alpha = 0.5f;
                     }
                     else
                     {
-                        dir = sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
+                        dir = sample_sphere(du1, du2, (Vec<D> *)nullptr);
                         dirPdf = Dims<D>::sphere_pdf();
                     }
                     float dist = R_B;
@@ -349,7 +477,7 @@ namespace
                         if (rr.hit)
                             dist = dm_fmin(rr.t, dist);
                     }
-                    const float r = green_sample_radius(R_B, S.seed, (uint32_t)pixel, (uint32_t)sample, (uint32_t)depth, q, (Vec<D> *)nullptr);
+                    const float r = green_sample_radius(R_B, dr, (Vec<D> *)nullptr);
                     if (r <= dist)
                     {
                         float w3[3] = {x[0] + r * dir[0], x[1] + r * dir[1], 0.0f};
@@ -370,8 +498,11 @@ namespace
                 // ---- neumann boundary sample (integrator.cu:318-445)
                 if (sn)
                 {
-                    const Philox4 q = wost_rng(S.seed, (uint32_t)pixel, (uint32_t)sample, (uint32_t)depth, WOST_RNG_NEUMANN, 0);
-                    const float u0 = u32_to_unit_float(q.x), u1 = u32_to_unit_float(q.y), u2 = u32_to_unit_float(q.z);
+                    // float u[DIM] filled by DIM draws; the 2D code reads u[2] past the array, ignored by sample_on_object<2> (:343-365)
+                    dr.begin(WOST_RNG_NEUMANN, 0);
+                    const float u0 = dr.next();
+                    const float u1 = dr.next();
+                    const float u2 = D == 3 ? dr.next() : 0.0f;
                     int obj;
                     float pdf;
                     sample_in_sphere(*sn, x, R_B, u0, obj, pdf);
@@ -420,12 +551,14 @@ namespace
 
                 // ---- one-step walk (integrator.cu:447-526)
                 {
-                    const Philox4 q = wost_rng(S.seed, (uint32_t)pixel, (uint32_t)sample, (uint32_t)depth, WOST_RNG_WALK, 0);
+                    dr.begin(WOST_RNG_WALK, 0);
+                    float wu1, wu2;
+                    draw_dir(wu1, wu2);
                     Vec<D> cur = x, dir;
                     float pdf, alpha = 1.0f;
                     if (onN)
                     {
-                        dir = to_world(nN, sample_hemisphere_local(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr));
+                        dir = to_world(nN, sample_hemisphere_local(wu1, wu2, (Vec<D> *)nullptr));
                         pdf = Dims<D>::hemi_pdf();
                         alpha = 0.5f;
                         for (int k = 0; k < D; ++k)
@@ -433,7 +566,7 @@ namespace
                     }
                     else
                     {
-                        dir = sample_sphere(u32_to_unit_float(q.x), u32_to_unit_float(q.y), (Vec<D> *)nullptr);
+                        dir = sample_sphere(wu1, wu2, (Vec<D> *)nullptr);
                         pdf = Dims<D>::sphere_pdf();
                     }
                     Vec<D> next, normal;

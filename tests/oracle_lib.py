@@ -242,6 +242,11 @@ class Oracle(_GeomLib):
     def set_math_mode(self, mode):
         self.lib.orc_set_math_mode(int(mode))
 
+    def set_rng_mode(self, mode):
+        """0 = Philox (product stream), 1 = the reference's per-pixel PCG32 (uniform walker only)"""
+        self.lib.orc_set_rng_mode.argtypes = [c_int]
+        self.lib.orc_set_rng_mode(int(mode))
+
     def used_morton64(self, scene):
         return bool(self.lib.orc_used_morton64(scene.h))
 
