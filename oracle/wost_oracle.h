@@ -26,6 +26,7 @@ extern "C"
      * consumption order (core/sampler.h:10-103, integrator/uniform/integrator.cu:72-77), to compare orc_solve_uniform
      * field-for-field with the reference's own CUDA build (tests/golden/b1_*.npz) */
     void orc_set_rng_mode(int mode);
+    void orc_pcg32_probe(uint64_t initstate, uint64_t initseq, int64_t delta, int n, uint32_t *out); /* PCG32 known answers */
 
     /* ---- geometry ---- */
     void *orc_scene_create(int dim, const float *verts, int nverts, const int *idx, int nprims);

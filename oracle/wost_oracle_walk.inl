@@ -633,6 +633,16 @@ extern "C"
             *steps = total.load();
     }
 
+    // known-answer probe: setSeed(initstate, initseq), advance(delta), then n raw 32-bit outputs
+    void orc_pcg32_probe(uint64_t initstate, uint64_t initseq, int64_t delta, int n, uint32_t *out)
+    {
+        Pcg32 g;
+        g.set_seed(initstate, initseq);
+        g.advance(delta);
+        for (int i = 0; i < n; ++i)
+            out[i] = g.next_uint();
+    }
+
     void orc_eval_point(const orc_problem_desc *p, const orc_settings *s, int pixel, float *out)
     {
         if (p->dim == 2)
