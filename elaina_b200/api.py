@@ -284,6 +284,13 @@ class _Integrator:
         check(_lib.load().wost_film_download(self.h, channel, _p(out)))
         return out
 
+    def film_stderr(self):
+        """(H, W, 3) measured standard error of the solution of the last solve (wost_film_stderr); exact per-pixel sample
+        standard error when the integrator was created with spp_batch == samples_per_pixel."""
+        out = np.zeros((self.settings.frame_h, self.settings.frame_w, 3), np.float32)
+        check(_lib.load().wost_film_stderr(self.h, _p(out)))
+        return out
+
     def film_device_ptr(self, channel=CH_SOLUTION):
         p = c_void_p()
         check(_lib.load().wost_film_device_ptr(self.h, channel, ctypes.byref(p)))

@@ -45,7 +45,7 @@ namespace wost
         float T[3]; // contributions of the walk so far
     };
     template <int D>
-    WOST_DEV void g_load(const GQueue &q, size_t i, GItem<D> &it)
+    WOST_DEV void g_load(const GQueue &q, size_t i, const uint32_t *active, GItem<D> &it)
     {
         const float4 a = q.q0[i], b = q.q1[i], c = q.q2[i];
         it.w.x[0] = a.x, it.w.x[1] = a.y;
@@ -56,7 +56,8 @@ namespace wost
         if (D == 3)
             it.w.nN[D - 1] = b.z;
         it.R_B = b.w;
-        it.w.pixel = __float_as_uint(c.x);
+        it.w.ai = __float_as_uint(c.x);
+        it.w.pixel = __ldg(active + it.w.ai);
         const uint32_t sf = __float_as_uint(c.y);
         it.w.sample = sf & 0x7fffffffu;
         it.w.onN = (sf >> 31) != 0;
@@ -68,11 +69,11 @@ namespace wost
     {
         q.q0[i] = make_float4(it.w.x[0], it.w.x[1], D == 3 ? it.w.x[D - 1] : 0.0f, it.w.thp);
         q.q1[i] = make_float4(it.w.nN[0], it.w.nN[1], D == 3 ? it.w.nN[D - 1] : 0.0f, it.R_B);
-        q.q2[i] = make_float4(__uint_as_float(it.w.pixel), __uint_as_float(it.w.sample | (it.w.onN ? 0x80000000u : 0u)), it.T[0], it.T[1]);
+        q.q2[i] = make_float4(__uint_as_float(it.w.ai), __uint_as_float(it.w.sample | (it.w.onN ? 0x80000000u : 0u)), it.T[0], it.T[1]);
         q.q3[i] = it.T[2];
     }
 
-    // record / training-set field offsets (in units of [kMaxTrainDepth][npix] resp. [cap] planes)
+    // record / training-set field offsets (in units of [kMaxTrainDepth][n_active] resp. [cap] planes)
     template <int D>
     struct RecLayout
     {
@@ -94,8 +95,8 @@ namespace wost
         uint32_t sample0;
         int batch_samples;
         uint32_t depth;
-        float4 *acc; // [slot][pixel]
-        int npix;
+        float4 *acc; // [slot][active rank]
+        int slot0;   // accumulator slot of sample0 (training batches of one sample rotate through the slots)
         int max_depth;
         int *overflow;
         // guiding
@@ -112,7 +113,7 @@ namespace wost
     // closest-point query + separate / boundary / source / Neumann stages of the point the walk has just reached.
     // Warp-synchronous: every lane calls it; lanes without a walk pass valid = false. Returns true when the walk goes on.
     template <int D>
-    WOST_DEV bool g_arrive(const WalkCtx<D> &c, GItem<D> &it, uint32_t depth, SmemStack &st, float4 *acc_base, uint32_t sample0, int npix, bool valid)
+    WOST_DEV bool g_arrive(const WalkCtx<D> &c, GItem<D> &it, uint32_t depth, SmemStack &st, float4 *acc_base, uint32_t sample0, int n_active, bool valid)
     {
         float R_D = dm_inf();
         uint32_t pos = kInvalid;
@@ -121,7 +122,7 @@ namespace wost
         if (!valid)
             return false;
         PixelAccT<true> acc;
-        acc.init(reinterpret_cast<float *>(acc_base + (size_t)(it.w.sample - sample0) * npix + it.w.pixel));
+        acc.init(reinterpret_cast<float *>(acc_base + (size_t)(it.w.sample - sample0) * n_active + it.w.ai));
         acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
         const bool alive = walk_step_contrib<D>(c, it.w, depth, st, acc, R_D, pos, 1.0f, it.R_B);
         acc.flush();
@@ -133,7 +134,7 @@ namespace wost
     WOST_DEV void g_record(const GArgs &a, const GItem<D> &it, const Vec<D> &dir, float pdf, uint32_t depth)
     {
         using L = RecLayout<D>;
-        const size_t plane = (size_t)kMaxTrainDepth * a.npix, o = (size_t)depth * a.npix + it.w.pixel;
+        const size_t plane = (size_t)kMaxTrainDepth * a.n_active, o = (size_t)depth * a.n_active + it.w.ai;
 #pragma unroll
         for (int k = 0; k < D; ++k)
         {
@@ -147,7 +148,7 @@ namespace wost
         for (int ch = 0; ch < 3; ++ch)
             a.rec[(L::kBase + ch) * plane + o] = it.T[ch];
         a.rec_onN[o] = it.w.onN ? 1 : 0;
-        a.rec_count[it.w.pixel] = (int)depth + 1;
+        a.rec_count[it.w.ai] = (int)depth + 1;
     }
     template <int D>
     WOST_DEV void g_finalize(const GArgs &a, const GItem<D> &it)
@@ -156,7 +157,7 @@ namespace wost
         {
 #pragma unroll
             for (int ch = 0; ch < 3; ++ch)
-                a.total[(size_t)ch * a.npix + it.w.pixel] = it.T[ch];
+                a.total[(size_t)ch * a.n_active + it.w.ai] = it.T[ch];
         }
     }
     // warp-aggregated append of the survivors of this warp
@@ -200,7 +201,7 @@ namespace wost
         NearestTrav<D> t;
         bool has = false, exhausted = false, trav = false;
         unsigned int my_steps = 0;
-        it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
+        it.w.pixel = 0, it.w.ai = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
         it.T[0] = it.T[1] = it.T[2] = 0.0f;
 #pragma unroll
         for (int k = 0; k < D; ++k)
@@ -216,7 +217,7 @@ namespace wost
                 if (!trav && has)
                 {
                     PixelAccT<true> acc;
-                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
+                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0 + (uint32_t)a.slot0) * a.n_active + it.w.ai));
                     acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
                     on = walk_step_contrib<D, F>(c, it.w, a.depth, st, acc, nearest_distance(t), t.win, 1.0f, it.R_B);
                     acc.flush();
@@ -245,6 +246,7 @@ namespace wost
                             {
                                 const uint32_t sj = (uint32_t)(i / a.n_active);
                                 const long long ai = i - (long long)sj * a.n_active;
+                                it.w.ai = (uint32_t)ai;
                                 it.w.pixel = __ldg(a.active + ai);
                                 it.w.sample = a.sample0 + sj;
                                 it.w.x = eval_point(c, it.w.pixel);
@@ -261,7 +263,7 @@ namespace wost
                                 t.best = __uint_as_float(f.y);
                             }
                             else
-                                g_load<D>(a.in, (size_t)i, it);
+                                g_load<D>(a.in, (size_t)i, a.active, it);
                             has = true;
                             ++my_steps;
                             if (!First)
@@ -374,10 +376,10 @@ namespace wost
             const bool valid = i < n;
             GItem<D> it;
             if (valid)
-                g_load<D>(a.in, (size_t)i, it);
+                g_load<D>(a.in, (size_t)i, a.active, it);
             else
             {
-                it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
+                it.w.pixel = 0, it.w.ai = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
                 it.T[0] = it.T[1] = it.T[2] = 0.0f;
 #pragma unroll
                 for (int k = 0; k < D; ++k)
@@ -439,7 +441,7 @@ namespace wost
         float rd = dm_inf(); // closest distance at the point the walk is about to leave (upper-bounds the next query)
         bool win_known = false; // t.win is the closest primitive of the point the walk is about to leave
         unsigned int my_steps = 0;
-        it.w.pixel = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
+        it.w.pixel = 0, it.w.ai = 0, it.w.sample = a.sample0, it.w.thp = 0.0f, it.w.onN = false, it.R_B = 0.0f;
         it.T[0] = it.T[1] = it.T[2] = 0.0f;
 #pragma unroll
         for (int k = 0; k < D; ++k)
@@ -454,7 +456,7 @@ namespace wost
                 if (!trav && has && need_contrib)
                 {
                     PixelAccT<true> acc;
-                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0) * a.npix + it.w.pixel));
+                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(it.w.sample - a.sample0 + (uint32_t)a.slot0) * a.n_active + it.w.ai));
                     acc.tot[0] = it.T[0], acc.tot[1] = it.T[1], acc.tot[2] = it.T[2];
                     rd = nearest_distance(t);
                     win_known = true;
@@ -482,7 +484,7 @@ namespace wost
                         const int i = base + __popc(want_mask & ((1u << lane) - 1u));
                         if (i < njobs)
                         {
-                            g_load<D>(a.in, (size_t)i, it);
+                            g_load<D>(a.in, (size_t)i, a.active, it);
                             depth = a.depth;
                             has = true;
                             rd = c.neu.nprims == 0 ? it.R_B : dm_inf(); // R_B = max(1e-4, R_D) when there is no Neumann mesh
@@ -591,11 +593,11 @@ namespace wost
     // ---- walk records -> training set (generate_training_data, guided/train.h:422-471), deterministic order:
     // samples are laid out by (position in the active-pixel list, record depth) through an exclusive scan.
     template <int D>
-    WOST_DEV bool g_sample_of_record(const WalkCtx<D> &c, const float *rec, const uint8_t *rec_onN, const float *total, int npix, uint32_t pixel, int d,
+    WOST_DEV bool g_sample_of_record(const WalkCtx<D> &c, const float *rec, const uint8_t *rec_onN, const float *total, int n_active, uint32_t ai, int d,
                                      Vec<D> &pos, TrainSample<D> &t)
     {
         using L = RecLayout<D>;
-        const size_t plane = (size_t)kMaxTrainDepth * npix, o = (size_t)d * npix + pixel;
+        const size_t plane = (size_t)kMaxTrainDepth * n_active, o = (size_t)d * n_active + ai;
 #pragma unroll
         for (int k = 0; k < D; ++k)
         {
@@ -611,7 +613,7 @@ namespace wost
 #pragma unroll
         for (int ch = 0; ch < 3; ++ch)
         {
-            const float sol = total[(size_t)ch * npix + pixel] - rec[(L::kBase + ch) * plane + o];
+            const float sol = total[(size_t)ch * n_active + ai] - rec[(L::kBase + ch) * plane + o];
             float v = 0.0f;
             if (dm_abs(thp) > kMEps)
                 v = dm_div(sol, thp);
@@ -627,7 +629,7 @@ namespace wost
         return ok && !bad;
     }
     template <int D>
-    __global__ void k_g_count_samples(const __grid_constant__ WalkCtx<D> c, const uint32_t *active, int n_active, int npix, const float *rec,
+    __global__ void k_g_count_samples(const __grid_constant__ WalkCtx<D> c, int n_active, const float *rec,
                                       const uint8_t *rec_onN, const int *rec_count, const float *total, int *counts)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -636,19 +638,18 @@ namespace wost
         int cnt = 0;
         if (i < n_active)
         {
-            const uint32_t pixel = active[i];
-            const int n = min(rec_count[pixel], kMaxTrainDepth);
+            const int n = min(rec_count[i], kMaxTrainDepth);
             for (int d = 0; d < n; ++d)
             {
                 Vec<D> pos;
                 TrainSample<D> t;
-                cnt += g_sample_of_record<D>(c, rec, rec_onN, total, npix, pixel, d, pos, t) ? 1 : 0;
+                cnt += g_sample_of_record<D>(c, rec, rec_onN, total, n_active, (uint32_t)i, d, pos, t) ? 1 : 0;
             }
         }
         counts[i] = cnt; // counts[n_active] = 0 so that the exclusive scan ends with the total
     }
     template <int D>
-    __global__ void k_g_scatter_samples(const __grid_constant__ WalkCtx<D> c, const uint32_t *active, int n_active, int npix, const float *rec,
+    __global__ void k_g_scatter_samples(const __grid_constant__ WalkCtx<D> c, int n_active, const float *rec,
                                         const uint8_t *rec_onN, const int *rec_count, const float *total, const int *offsets, int cap, float *smp,
                                         uint8_t *smp_onN, TrainCtl *ctl)
     {
@@ -658,14 +659,13 @@ namespace wost
             ctl->n_samples = min(offsets[n_active], cap);
         if (i >= n_active)
             return;
-        const uint32_t pixel = active[i];
-        const int n = min(rec_count[pixel], kMaxTrainDepth);
+        const int n = min(rec_count[i], kMaxTrainDepth);
         int o = offsets[i];
         for (int d = 0; d < n; ++d)
         {
             Vec<D> pos;
             TrainSample<D> t;
-            if (!g_sample_of_record<D>(c, rec, rec_onN, total, npix, pixel, d, pos, t))
+            if (!g_sample_of_record<D>(c, rec, rec_onN, total, n_active, (uint32_t)i, d, pos, t))
                 continue;
             if (o < cap)
             {
@@ -1202,7 +1202,7 @@ namespace wost
                 return WOST_ERR_CUDA;
         }
         GuidedBuffers &g = it->gb;
-        const size_t npix = (size_t)it->npix;
+        const size_t npix = (size_t)std::max(1, it->n_active); // walk records are indexed by active rank: sized by the shard, not the frame
         const int planes = 3 * D + 5;
         g.cap = (int)std::min<size_t>((size_t)kMaxTrainDepth * std::max(1, it->n_active), (size_t)1 << 30);
         if (g.rec.alloc((size_t)planes * kMaxTrainDepth * npix) != cudaSuccess || g.rec_onN.alloc((size_t)kMaxTrainDepth * npix) != cudaSuccess ||
@@ -1299,11 +1299,11 @@ namespace wost
         }
         int *opt_steps = &n.ctl.ptr->opt_steps[0];
         k_g_frame_ctl<<<1, 1, 0, st>>>(n.ctl.ptr, opt_steps, 0);
-        k_g_count_samples<D><<<div_up(it->n_active + 1, 256), 256, 0, st>>>(ctx, it->d_active.ptr, it->n_active, it->npix, g.rec.ptr, g.rec_onN.ptr,
+        k_g_count_samples<D><<<div_up(it->n_active + 1, 256), 256, 0, st>>>(ctx, it->n_active, g.rec.ptr, g.rec_onN.ptr,
                                                                                g.rec_count.ptr, g.total.ptr, g.sample_off.ptr);
         size_t tb = g.scan_tmp_bytes;
         WOST_CUDA_TRY(cub::DeviceScan::ExclusiveSum(g.scan_tmp.ptr, tb, g.sample_off.ptr, g.sample_off.ptr, it->n_active + 1, st));
-        k_g_scatter_samples<D><<<div_up(it->n_active, 256), 256, 0, st>>>(ctx, it->d_active.ptr, it->n_active, it->npix, g.rec.ptr, g.rec_onN.ptr,
+        k_g_scatter_samples<D><<<div_up(std::max(1, it->n_active), 256), 256, 0, st>>>(ctx, it->n_active, g.rec.ptr, g.rec_onN.ptr,
                                                                              g.rec_count.ptr, g.total.ptr, g.sample_off.ptr, g.cap, g.smp.ptr, g.smp_onN.ptr, n.ctl.ptr);
         it->launches += 4;
         // with a gradient all-reduce every rank must issue the same number of collectives, whatever its own sample count
@@ -1375,10 +1375,11 @@ namespace wost
         WOST_DISPATCH_K0(D, n.k0, (grid_bounce = bounce_grid<D, K0_>()));
         const int max_train_depth = std::min(kMaxTrainDepth, it->s.max_train_depth > 0 ? it->s.max_train_depth : 3);
 
-        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * std::max(1, it->n_active), st));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0, it->step_launches = 0, it->step_kernel_ms = 0.0f;
         it->train_samples = 0, it->train_steps = 0;
+        it->slot_n.assign((size_t)S, 0);
         // optional per-kernel-class device timing (WOST_PROFILE=1): CUDA events around every launch of the solve
         const bool prof = getenv("WOST_PROFILE") != nullptr;
         size_t prof_used = 0;
@@ -1421,10 +1422,24 @@ namespace wost
             k_first_hit<D, false><<<grid, kGBlock, stack_smem, st>>>(ctx, it->d_active.ptr, it->n_active, it->d_first.ptr, it->d_overflow.ptr);
             ++it->launches;
         }
-        for (size_t bi = 0; it->n_active > 0 && bi < batches.size(); ++bi)
+        // A rank without active pixels (all its row tiles masked, or fewer tiles than ranks) launches no walk kernels but still
+        // takes part in every gradient all-reduce of the training phase: it contributes a zero slab with valid = 0.
+        const bool walks = it->n_active > 0;
+        for (size_t bi = 0; (walks || it->allreduce) && bi < batches.size(); ++bi)
         {
             const int s0 = batches[bi].first, Sb = batches[bi].second;
             const bool training = s0 < it->s.train_spp_count;
+            if (!walks)
+            {
+                if (training)
+                {
+                    WOST_CUDA_TRY(cudaMemsetAsync(g.rec_count.ptr, 0, sizeof(int), st));
+                    const wost_status rc = train_frame<D>(it, ctx);
+                    if (rc != WOST_OK)
+                        return rc;
+                }
+                continue;
+            }
             // solveImpl :991-996: after trainSppCount samples switch to the guiding-phase settings
             const int maxGuided = training ? it->s.max_guided_depth_training : it->s.max_guided_depth_guiding;
             const float ufrac = training ? it->s.uniform_fraction_training : it->s.uniform_fraction_guiding;
@@ -1432,7 +1447,7 @@ namespace wost
             WOST_CUDA_TRY(cudaMemsetAsync(it->d_counts.ptr, 0, sizeof(int) * (size_t)(3 * (maxd + 2)), st));
             WOST_CUDA_TRY(cudaMemsetAsync(it->d_cursor64.ptr, 0, sizeof(unsigned long long), st));
             if (training)
-                WOST_CUDA_TRY(cudaMemsetAsync(g.rec_count.ptr, 0, sizeof(int) * (size_t)it->npix, st));
+                WOST_CUDA_TRY(cudaMemsetAsync(g.rec_count.ptr, 0, sizeof(int) * (size_t)std::max(1, it->n_active), st));
             WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi], st));
             GArgs a;
             memset(&a, 0, sizeof(a));
@@ -1440,7 +1455,10 @@ namespace wost
             a.active = it->d_active.ptr, a.n_active = it->n_active;
             a.first = it->d_first.ptr;
             a.sample0 = (uint32_t)s0, a.batch_samples = Sb;
-            a.acc = it->d_acc.ptr, a.npix = it->npix, a.max_depth = maxd, a.overflow = it->d_overflow.ptr;
+            a.acc = it->d_acc.ptr, a.max_depth = maxd, a.overflow = it->d_overflow.ptr;
+            a.slot0 = training ? s0 % S : 0; // a training batch is one sample: rotate it through the S accumulator slots
+            for (int j = 0; j < Sb; ++j)
+                ++it->slot_n[(size_t)(a.slot0 + j)];
             a.training = training ? 1 : 0;
             a.max_train_depth = max_train_depth;
             a.uniform_fraction = ufrac;
@@ -1507,8 +1525,7 @@ namespace wost
                 if (frc != WOST_OK)
                     return frc;
             }
-            // the accumulator slots are summed into slot 0 between batches of different sizes? No: slot s of every batch
-            // adds to acc[s]; k_resolve sums all S slots at the end, so a training batch (1 sample) simply uses slot 0.
+            // slot s of every batch adds to acc[s]; k_resolve sums all S slots at the end
         }
         launch_resolve(it, S, (float)spp);
         ++it->launches;
@@ -1524,7 +1541,7 @@ namespace wost
         WOST_CUDA_TRY(cudaStreamSynchronize(st));
         if (walk_steps)
             *walk_steps = h_steps;
-        for (size_t bi = 0; it->n_active > 0 && bi < batches.size(); ++bi)
+        for (size_t bi = 0; walks && bi < batches.size(); ++bi)
         {
             float f = 0.0f;
             WOST_CUDA_TRY(cudaEventElapsedTime(&f, it->batch_ev[2 * bi], it->batch_ev[2 * bi + 1]));

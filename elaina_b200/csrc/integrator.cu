@@ -22,11 +22,12 @@ namespace wost
 {
     constexpr int kWalkBlock = 128;
 
-    WOST_DEV void load_item(const QueueView &q, size_t i, WalkState<2> &w)
+    WOST_DEV void load_item(const QueueView &q, size_t i, const uint32_t *active, WalkState<2> &w)
     {
         const float4 a = q.a[i], b = q.b[i];
         w.x[0] = a.x, w.x[1] = a.y;
-        w.pixel = __float_as_uint(a.z);
+        w.ai = __float_as_uint(a.z);
+        w.pixel = __ldg(active + w.ai);
         const uint32_t sf = __float_as_uint(a.w);
         w.sample = sf & 0x7fffffffu;
         w.onN = (sf >> 31) != 0;
@@ -35,24 +36,25 @@ namespace wost
     }
     WOST_DEV void store_item(const QueueView &q, size_t i, const WalkState<2> &w)
     {
-        q.a[i] = make_float4(w.x[0], w.x[1], __uint_as_float(w.pixel), __uint_as_float(w.sample | (w.onN ? 0x80000000u : 0u)));
+        q.a[i] = make_float4(w.x[0], w.x[1], __uint_as_float(w.ai), __uint_as_float(w.sample | (w.onN ? 0x80000000u : 0u)));
         q.b[i] = make_float4(w.nN[0], w.nN[1], w.thp, 0.0f);
     }
-    WOST_DEV void load_item(const QueueView &q, size_t i, WalkState<3> &w)
+    WOST_DEV void load_item(const QueueView &q, size_t i, const uint32_t *active, WalkState<3> &w)
     {
         const float4 a = q.a[i], b = q.b[i];
         const uint32_t sf = q.c[i];
         w.x[0] = a.x, w.x[1] = a.y, w.x[2] = a.z;
         w.thp = a.w;
         w.nN[0] = b.x, w.nN[1] = b.y, w.nN[2] = b.z;
-        w.pixel = __float_as_uint(b.w);
+        w.ai = __float_as_uint(b.w);
+        w.pixel = __ldg(active + w.ai);
         w.sample = sf & 0x7fffffffu;
         w.onN = (sf >> 31) != 0;
     }
     WOST_DEV void store_item(const QueueView &q, size_t i, const WalkState<3> &w)
     {
         q.a[i] = make_float4(w.x[0], w.x[1], w.x[2], w.thp);
-        q.b[i] = make_float4(w.nN[0], w.nN[1], w.nN[2], __uint_as_float(w.pixel));
+        q.b[i] = make_float4(w.nN[0], w.nN[1], w.nN[2], __uint_as_float(w.ai));
         q.c[i] = w.sample | (w.onN ? 0x80000000u : 0u);
     }
 
@@ -68,8 +70,7 @@ namespace wost
         uint32_t sample0; // first sample of the batch
         int batch_samples;
         uint32_t depth;
-        float4 *acc; // [slot][pixel]
-        int npix;
+        float4 *acc; // [slot][active rank]
         int last_depth; // 1: survivors are dropped (depth == maxWalkingDepth-1)
         int *overflow;
     };
@@ -102,7 +103,8 @@ namespace wost
                 if (First)
                 {
                     const uint32_t sj = (uint32_t)(i / a.n_active);
-                    w.pixel = __ldg(a.active + (i - (long long)sj * a.n_active));
+                    w.ai = (uint32_t)(i - (long long)sj * a.n_active);
+                    w.pixel = __ldg(a.active + w.ai);
                     w.sample = a.sample0 + sj;
                     w.x = eval_point(c, w.pixel);
                     w.thp = 1.0f;
@@ -112,11 +114,11 @@ namespace wost
                         w.nN[k] = 0.0f;
                 }
                 else
-                    load_item(a.in, (size_t)i, w);
+                    load_item(a.in, (size_t)i, a.active, w);
             }
             else
             {
-                w.pixel = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
+                w.pixel = 0, w.ai = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
 #pragma unroll
                 for (int k = 0; k < D; ++k)
                     w.x[k] = w.nN[k] = 0.0f;
@@ -124,7 +126,7 @@ namespace wost
             {
                 // every lane of the warp enters the step (the closest-point traversal is warp-synchronous)
                 PixelAcc acc;
-                acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
+                acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.n_active + w.ai));
                 alive = walk_step_uniform<D, RefOrder>(c, w, a.depth, st, acc, valid);
                 acc.flush();
             }
@@ -167,8 +169,7 @@ namespace wost
         int n_active;
         uint32_t sample0;
         int batch_samples;
-        float4 *acc; // [slot][pixel]
-        int npix;
+        float4 *acc; // [slot][active rank]
         int max_depth;
         int refill_threshold;
         int *cursor;
@@ -194,7 +195,7 @@ namespace wost
         bool has_walk = false, exhausted = false, trav = false, fresh = false;
         unsigned int my_steps = 0;
         float bound = dm_inf(); // upper bound of the next closest-point distance: R_D of this step + the distance moved
-        w.pixel = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
+        w.pixel = 0, w.ai = 0, w.sample = a.sample0, w.thp = 0.0f, w.onN = false;
 #pragma unroll
         for (int k = 0; k < D; ++k)
             w.x[k] = w.nN[k] = 0.0f;
@@ -208,7 +209,8 @@ namespace wost
                 if (!trav && has_walk)
                 {
                     PixelAcc acc;
-                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.npix + w.pixel));
+                    acc.init(reinterpret_cast<float *>(a.acc + (size_t)(w.sample - a.sample0) * a.n_active + w.ai));
+                    w.pixel = __ldg(a.active + w.ai); // only the tail needs the pixel id (Philox key): not live across the traversal trips
                     const Vec<D> x0 = w.x;
                     const float R_D = nearest_distance(t);
                     const bool alive = walk_step_tail<D, F>(c, w, depth, st, acc, R_D, t.win);
@@ -239,9 +241,9 @@ namespace wost
                         {
                             const uint32_t sj = (uint32_t)(i / a.n_active);
                             const long long ai = i - (long long)sj * a.n_active;
-                            w.pixel = __ldg(a.active + ai);
+                            w.ai = (uint32_t)ai;
                             w.sample = a.sample0 + sj;
-                            w.x = eval_point(c, w.pixel);
+                            w.x = eval_point(c, __ldg(a.active + ai));
                             w.thp = 1.0f;
                             w.onN = false;
 #pragma unroll
@@ -283,26 +285,64 @@ namespace wost
             atomicAdd(a.steps, (unsigned long long)ws);
     }
 
-    // solution/spp -> Film (integrator.cu:614-620): {r,g,b,1, weight 1}; slots are summed in slot order
-    __global__ void k_resolve(int npix, int nslots, const float4 *acc, float inv_spp, const uint32_t *owned_begin_end, float *film)
+    // solution/spp -> Film (integrator.cu:614-620): {r,g,b,1, weight 1}. Accumulators are indexed by the active rank of
+    // the pixel (shard-sized); slots are summed in slot order and scattered to the pixel's film entry. The film entries of
+    // pixels this shard does not own keep their initial {0,0,0,1,1} (k_film_init).
+    // se != nullptr: also the standard error of the pixel mean from the slot means (slot s holds slot_n[s] samples of the
+    // pixel): se^2 = sum_s n_s (m_s - m)^2 / ((S_used - 1) * spp) -- the exact sample variance / spp when every slot holds one sample.
+    __global__ void k_resolve(int n_active, int nslots, const float4 *acc, const uint32_t *active, float spp, float *film, const int *slot_n, float *se)
     {
-        const int p = blockIdx.x * blockDim.x + threadIdx.x;
-        if (p >= npix)
+        const int ai = blockIdx.x * blockDim.x + threadIdx.x;
+        if (ai >= n_active)
             return;
         float r = 0.0f, g = 0.0f, b = 0.0f;
         for (int s = 0; s < nslots; ++s)
         {
-            const float4 v = acc[(size_t)s * npix + p];
+            const float4 v = acc[(size_t)s * n_active + ai];
             r = r + v.x;
             g = g + v.y;
             b = b + v.z;
         }
+        const uint32_t p = active[ai];
         float *f = film + (size_t)p * 5;
-        f[0] = dm_div(r, inv_spp);
-        f[1] = dm_div(g, inv_spp);
-        f[2] = dm_div(b, inv_spp);
+        f[0] = dm_div(r, spp);
+        f[1] = dm_div(g, spp);
+        f[2] = dm_div(b, spp);
         f[3] = 1.0f;
         f[4] = 1.0f;
+        if (se)
+        {
+            const double m[3] = {(double)r / spp, (double)g / spp, (double)b / spp};
+            double q[3] = {0.0, 0.0, 0.0};
+            int used = 0;
+            for (int s = 0; s < nslots; ++s)
+            {
+                const int n = slot_n[s];
+                if (n <= 0)
+                    continue;
+                ++used;
+                const float4 v = acc[(size_t)s * n_active + ai];
+                const double d0 = (double)v.x / n - m[0], d1 = (double)v.y / n - m[1], d2 = (double)v.z / n - m[2];
+                q[0] += n * d0 * d0, q[1] += n * d1 * d1, q[2] += n * d2 * d2;
+            }
+            for (int ch = 0; ch < 3; ++ch)
+                se[(size_t)p * 3 + ch] = used > 1 ? (float)sqrt(q[ch] / ((double)(used - 1) * spp)) : 0.0f;
+        }
+    }
+    __global__ void k_film_init(int npix, float *film)
+    {
+        const int p = blockIdx.x * blockDim.x + threadIdx.x;
+        if (p >= npix)
+            return;
+        float *f = film + (size_t)p * 5;
+        f[0] = f[1] = f[2] = 0.0f;
+        f[3] = f[4] = 1.0f;
+    }
+
+    void launch_resolve(wost_integrator *it, int nslots, float spp)
+    {
+        if (it->n_active > 0)
+            k_resolve<<<div_up(it->n_active, 256), 256, 0, it->stream>>>(it->n_active, nslots, it->d_acc.ptr, it->d_active.ptr, spp, it->film[WOST_CH_SOLUTION].ptr, nullptr, nullptr);
     }
 
     wost_status emit_frames(wost_integrator *it, int sample_id)
@@ -311,7 +351,7 @@ namespace wost
         if (!kinds)
             return WOST_OK;
         cudaStream_t st = it->stream;
-        k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, it->spp_batch, it->d_acc.ptr, (float)(sample_id + 1), nullptr, it->film[WOST_CH_SOLUTION].ptr);
+        launch_resolve(it, it->spp_batch, (float)(sample_id + 1));
         ++it->launches;
         it->frame_host.resize((size_t)it->npix * 5);
         WOST_CUDA_TRY(cudaMemcpyAsync(it->frame_host.data(), it->film[WOST_CH_SOLUTION].ptr, sizeof(float) * 5 * (size_t)it->npix, cudaMemcpyDeviceToHost, st));
@@ -371,10 +411,6 @@ namespace wost
         }
     }
 
-    void launch_resolve(wost_integrator *it, int nslots, float spp)
-    {
-        k_resolve<<<div_up(it->npix, 256), 256, 0, it->stream>>>(it->npix, nslots, it->d_acc.ptr, spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
-    }
     template <int D, bool RefOrder>
     static wost_status solve_uniform(wost_integrator *it, uint64_t *walk_steps)
     {
@@ -394,11 +430,15 @@ namespace wost
         WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_step_uniform<D, false, RefOrder>, kWalkBlock, smem));
         const int grid_full = sm_count() * std::max(1, occ);
 
-        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * std::max(1, it->n_active), st));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0;
         it->step_launches = 0;
         it->step_kernel_ms = 0.0f;
+        it->slot_n.assign((size_t)S, 0);
+        for (int s0 = 0; s0 < spp; s0 += S)
+            for (int j = 0; j < std::min(S, spp - s0); ++j)
+                ++it->slot_n[(size_t)j];
         const int nbatches = it->n_active > 0 ? (spp + S - 1) / S : 0;
         while ((int)it->batch_ev.size() < 2 * nbatches)
         {
@@ -428,7 +468,6 @@ namespace wost
                     a.batch_samples = Sb;
                     a.depth = (uint32_t)depth;
                     a.acc = it->d_acc.ptr;
-                    a.npix = it->npix;
                     a.last_depth = (depth == maxd - 1) ? 1 : 0;
                     a.overflow = it->d_overflow.ptr;
                     if (depth == 0)
@@ -445,7 +484,7 @@ namespace wost
                 WOST_CUDA_TRY(cudaEventRecord(it->batch_ev[2 * bi + 1], st));
             }
         }
-        k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
+        launch_resolve(it, S, (float)spp);
         ++it->launches;
         WOST_CUDA_TRY(cudaGetLastError());
         unsigned long long h_steps = 0;
@@ -508,7 +547,7 @@ namespace wost
         int refill_threshold = kRefillThreshold;
         if (const char *e = getenv("WOST_REFILL_THRESHOLD")) // tuning knob (profiles/r1_notes.md)
             refill_threshold = std::max(1, std::min(32, atoi(e)));
-        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * it->npix, st));
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * std::max(1, it->n_active), st));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0;
         it->step_launches = 0;
@@ -521,6 +560,10 @@ namespace wost
             batches.emplace_back(s0, Sb);
             s0 += Sb;
         }
+        it->slot_n.assign((size_t)S, 0);
+        for (const auto &b : batches)
+            for (int j = 0; j < b.second; ++j)
+                ++it->slot_n[(size_t)j];
         const int nbatches = (int)batches.size();
         while ((int)it->batch_ev.size() < 2 * nbatches)
         {
@@ -551,7 +594,6 @@ namespace wost
             a.sample0 = (uint32_t)s0;
             a.batch_samples = Sb;
             a.acc = it->d_acc.ptr;
-            a.npix = it->npix;
             a.max_depth = it->s.max_walking_depth;
             a.refill_threshold = refill_threshold;
             a.cursor = it->d_counts.ptr;
@@ -570,7 +612,7 @@ namespace wost
                     return frc;
             }
         }
-        k_resolve<<<div_up(it->npix, 256), 256, 0, st>>>(it->npix, S, it->d_acc.ptr, (float)spp, nullptr, it->film[WOST_CH_SOLUTION].ptr);
+        launch_resolve(it, S, (float)spp);
         ++it->launches;
         WOST_CUDA_TRY(cudaGetLastError());
         unsigned long long h_steps = 0;
@@ -723,11 +765,15 @@ extern "C"
         std::vector<uint32_t> active;
         active.reserve(pe - pb);
         const uint8_t *mask = problem->desc.mask;
+        // frame-wide count of evaluated pixels: identical on every rank whatever its pixel range / shard (it sizes the
+        // data-parallel training batches, so that all ranks issue the same number of gradient all-reduces)
+        for (int p = 0; p < it->npix; ++p)
+            if (!mask || mask[p])
+                ++it->n_active_frame;
         for (int p = pb; p < pe; ++p)
         {
             if (mask && !mask[p])
                 continue;
-            ++it->n_active_frame;
             if (s.pixel_stride_rows > 0 && s.num_shards > 1)
             {
                 const int row = p / s.frame_w;
@@ -745,6 +791,8 @@ extern "C"
             S = (int)std::max<long long>(1, target / std::max(1, it->n_active));
         }
         S = std::max(1, std::min(S, s.samples_per_pixel));
+        // the walk kernels claim jobs through 32-bit cursors: keep n_active * S below 2^31 (more samples simply take more batches)
+        S = (int)std::min<long long>(S, std::max<long long>(1, ((1ll << 31) - 4096) / std::max(1, it->n_active)));
         it->spp_batch = S;
         it->queue_capacity = (size_t)std::max(1, it->n_active) * S;
         auto fail = [&](const char *msg)
@@ -765,13 +813,16 @@ extern "C"
         if (kind == WOST_GUIDED && (it->d_cursor64.alloc(1) != cudaSuccess || guided_alloc(it) != WOST_OK))
             return fail("guided buffer allocation");
         if (it->d_counts.alloc((size_t)3 * (s.max_walking_depth + 2)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
-            it->d_acc.alloc((size_t)S * it->npix) != cudaSuccess || it->d_overflow.alloc(1) != cudaSuccess)
+            it->d_acc.alloc((size_t)S * std::max(1, it->n_active)) != cudaSuccess || it->d_overflow.alloc(1) != cudaSuccess)
             return fail("buffer allocation");
         for (int c = 0; c < WOST_CH_COUNT; ++c)
         {
             if (it->film[c].alloc((size_t)it->npix * 5) != cudaSuccess)
                 return fail("film allocation");
-            cudaMemset(it->film[c].ptr, 0, sizeof(float) * (size_t)it->npix * 5);
+            if (c == WOST_CH_SOLUTION)
+                k_film_init<<<div_up(it->npix, 256), 256>>>(it->npix, it->film[c].ptr); // pixels outside the mask / shard: solution 0, weight 1
+            else
+                cudaMemset(it->film[c].ptr, 0, sizeof(float) * (size_t)it->npix * 5);
         }
         cudaMemset(it->d_overflow.ptr, 0, sizeof(int));
         if (cudaStreamCreateWithFlags(&it->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&it->ev0) != cudaSuccess ||
@@ -866,6 +917,35 @@ extern "C"
         if (!it || !out || channel < 0 || channel >= WOST_CH_COUNT)
             return WOST_ERR_INVALID;
         WOST_CUDA_TRY(cudaMemcpyAsync(out, it->film[channel].ptr, sizeof(float) * (size_t)it->npix * 5, cudaMemcpyDeviceToHost, it->stream));
+        WOST_CUDA_TRY(cudaStreamSynchronize(it->stream));
+        return WOST_OK;
+    }
+    wost_status wost_film_stderr(wost_integrator *it, float *out_se_rgb)
+    {
+        if (!it || !out_se_rgb)
+            return WOST_ERR_INVALID;
+        if (it->slot_n.empty())
+        {
+            set_last_error("wost_film_stderr: no solve has run on this integrator");
+            return WOST_ERR_INVALID;
+        }
+        const size_t n = (size_t)it->npix * 3;
+        if (it->d_se.count < n && it->d_se.alloc(n) != cudaSuccess)
+        {
+            set_last_error("wost_film_stderr: allocation failed");
+            return WOST_ERR_CUDA;
+        }
+        if (it->d_slot_n.upload(it->slot_n.data(), it->slot_n.size()) != cudaSuccess)
+        {
+            set_last_error("wost_film_stderr: upload failed");
+            return WOST_ERR_CUDA;
+        }
+        WOST_CUDA_TRY(cudaMemsetAsync(it->d_se.ptr, 0, sizeof(float) * n, it->stream));
+        if (it->n_active > 0)
+            k_resolve<<<div_up(it->n_active, 256), 256, 0, it->stream>>>(it->n_active, (int)it->slot_n.size(), it->d_acc.ptr, it->d_active.ptr,
+                                                                         (float)it->s.samples_per_pixel, it->film[WOST_CH_SOLUTION].ptr, it->d_slot_n.ptr, it->d_se.ptr);
+        WOST_CUDA_TRY(cudaGetLastError());
+        WOST_CUDA_TRY(cudaMemcpyAsync(out_se_rgb, it->d_se.ptr, sizeof(float) * n, cudaMemcpyDeviceToHost, it->stream));
         WOST_CUDA_TRY(cudaStreamSynchronize(it->stream));
         return WOST_OK;
     }

@@ -11,8 +11,9 @@ namespace wost
     // (integrator/uniform/workqueue.h:32-69, util/soac.cpp:302-508): one float4 column per 16 bytes of state, so a warp
     // moves 512 contiguous bytes per instruction; slots are claimed with ONE atomic per warp (ballot + popc), not one
     // per item, and the queue of bounce d+1 is written compacted, so later bounces only touch live walks.
-    //   2D: a = {x, y, bits(pixel), bits(sample | onN << 31)}   b = {nx, ny, thp, 0}
-    //   3D: a = {x, y, z, thp}   b = {nx, ny, nz, bits(pixel)}   c = sample | onN << 31
+    //   2D: a = {x, y, bits(ai), bits(sample | onN << 31)}   b = {nx, ny, thp, 0}
+    //   3D: a = {x, y, z, thp}   b = {nx, ny, nz, bits(ai)}   c = sample | onN << 31
+    // ai = rank of the pixel among the shard's active pixels (pixelId = active[ai])
     struct QueueView
     {
         float4 *a;
@@ -37,7 +38,10 @@ struct wost_integrator
     wost::DevBuf<uint32_t> qc[2];
     wost::DevBuf<int> d_counts; // [0..max_depth]: items of bounce d; [max_depth+1 ..]: claim cursors
     wost::DevBuf<unsigned long long> d_steps;
-    wost::DevBuf<float4> d_acc; // [slot][pixel] rgb accumulators
+    wost::DevBuf<float4> d_acc; // [slot][active rank] rgb accumulators (shard-sized: S * n_active)
+    std::vector<int> slot_n;    // samples of every pixel that went to accumulator slot s in the last solve (wost_film_stderr)
+    wost::DevBuf<int> d_slot_n;
+    wost::DevBuf<float> d_se;   // [pixel][rgb] standard error of the pixel mean, filled on request
     wost::DevBuf<float> film[WOST_CH_COUNT];
     wost::DevBuf<int> d_overflow;
     cudaStream_t stream = nullptr;

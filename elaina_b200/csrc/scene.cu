@@ -44,11 +44,12 @@ namespace wost
             static const bool on = getenv("WOST_NO_ALLOC_CACHE") == nullptr;
             return on;
         }
-        unsigned long long cache_key(size_t bytes)
+        unsigned long long cache_key(int dev, size_t bytes) { return ((unsigned long long)dev << 48) | (unsigned long long)bytes; }
+        int current_device()
         {
             int dev = 0;
             cudaGetDevice(&dev);
-            return ((unsigned long long)dev << 48) | (unsigned long long)bytes;
+            return dev;
         }
     } // namespace
     cudaError_t dev_alloc(void **ptr, size_t bytes)
@@ -57,7 +58,7 @@ namespace wost
         {
             AllocCache &c = alloc_cache();
             std::lock_guard<std::mutex> lock(c.mu);
-            auto it = c.free_blocks.find(cache_key(bytes));
+            auto it = c.free_blocks.find(cache_key(current_device(), bytes));
             if (it != c.free_blocks.end())
             {
                 *ptr = it->second;
@@ -86,9 +87,23 @@ namespace wost
             std::lock_guard<std::mutex> lock(c.mu);
             if (c.cached_bytes + bytes <= kCacheMaxBytes)
             {
-                // a parked block may be handed out again at once: no work of any stream may still touch it (cudaFree waits too)
+                // The block is parked under the device that OWNS it, which need not be the current one (wost_set_device is
+                // public: one process may drive several GPUs and destroy a handle while another device is current).
+                cudaPointerAttributes attr;
+                int owner = current_device();
+                if (cudaPointerGetAttributes(&attr, ptr) == cudaSuccess && attr.type == cudaMemoryTypeDevice)
+                    owner = attr.device;
+                else
+                    cudaGetLastError();
+                // a parked block may be handed out again at once: no work of any stream of its device may still touch it
+                // (cudaFree waits too)
+                const int cur = current_device();
+                if (owner != cur)
+                    cudaSetDevice(owner);
                 cudaDeviceSynchronize();
-                c.free_blocks.emplace(cache_key(bytes), ptr);
+                if (owner != cur)
+                    cudaSetDevice(cur);
+                c.free_blocks.emplace(cache_key(owner, bytes), ptr);
                 c.cached_bytes += bytes;
                 return;
             }

@@ -20,7 +20,8 @@ namespace wost
         Vec<D> x;       // current point
         Vec<D> nN;      // shading normal of the Neumann boundary the point sits on (if onN)
         float thp;      // throughput (a scalar: every factor applied to it is a scalar, oneStepWalk :521)
-        uint32_t pixel; // pixelId = x + y*W
+        uint32_t pixel; // pixelId = x + y*W (keys the Philox stream, locates the evaluation point)
+        uint32_t ai;    // rank of the pixel among this shard's active pixels: indexes accumulators / walk records (sized by the shard, not the frame)
         uint32_t sample;
         bool onN;
     };

@@ -165,6 +165,13 @@ extern "C"
     wost_status wost_render_channel(wost_integrator *it, int channel);
     /* Film (util/film.h:16-155): per pixel {r,g,b,a, weight}, index x + y*W, NOT flipped (files are flipped on save only) */
     wost_status wost_film_download(wost_integrator *it, int channel, float *out_rgbaw);
+    /* Standard error of the solution film of the last solve, per pixel and colour channel (W*H*3 floats, 0 for pixels this
+     * shard does not evaluate). Measured, not modelled: the accumulators keep one running sum per (slot, pixel) where a slot
+     * receives every spp_batch-th sample, so se^2 = sum_s n_s (m_s - m)^2 / ((S - 1) spp) over the slot means m_s; with
+     * spp_batch == samples_per_pixel every slot holds ONE sample and this is the exact sample variance / spp. The reference
+     * has no such output (its PixelState keeps only the running sum, integrator/uniform/workqueue.h:15-30); the statistical
+     * parity tests (|delta| <= 3 standard errors per pixel) need it. */
+    wost_status wost_film_stderr(wost_integrator *it, float *out_se_rgb);
     /* device pointer of the film of `channel` (W*H*5 floats) for NCCL gathers issued by the host language */
     wost_status wost_film_device_ptr(wost_integrator *it, int channel, void **d_ptr);
     /* counters of the last solve */
