@@ -264,11 +264,17 @@ def main():
     e2e_steps = 0
 
     def e2e_once():
+        t_ = [time.perf_counter()]
         p = make_problem()
+        t_.append(time.perf_counter())
         i2 = Integrator(p, settings)
+        t_.append(time.perf_counter())
         if guided and world > 1:
             wdist.install_gradient_allreduce(i2, dev)
         i2.solve()
+        t_.append(time.perf_counter())
+        if os.environ.get("WOST_BENCH_DEBUG"):
+            print("e2e stages ms: problem %.1f integrator %.1f solve %.1f (device %.1f)" % (1e3 * (t_[1] - t_[0]), 1e3 * (t_[2] - t_[1]), 1e3 * (t_[3] - t_[2]), i2.last_device_ms), file=sys.stderr, flush=True)
         if world > 1:
             # final film gather: shards own disjoint rows and write zeros elsewhere -> one NCCL sum
             ptr = i2.film_device_ptr()

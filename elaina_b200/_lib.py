@@ -102,6 +102,9 @@ SYMBOLS = [
     ("wost_render_channel", c_int, [c_void_p, c_int]),
     ("wost_film_download", c_int, [c_void_p, c_int, c_void_p]),
     ("wost_film_stderr", c_int, [c_void_p, c_void_p]),
+    ("wost_traversal_stats", c_int, [c_void_p, c_void_p, c_void_p, c_int]),
+    ("wost_debug_counters", c_int, [c_void_p, c_void_p]),
+    ("wost_scene_traversal_stats", c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     ("wost_film_device_ptr", c_int, [c_void_p, c_int, _PP(c_void_p)]),
     ("wost_last_launch_count", c_int, [c_void_p, _PP(c_u64)]),
     ("wost_last_step_kernel_time", c_int, [c_void_p, _PP(c_u64), _PP(c_float)]),

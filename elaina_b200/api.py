@@ -87,6 +87,12 @@ class Scene:
         return m, o
 
     # ---- queries (host buffers through the C ABI)
+    def traversal_stats(self, reset=True):
+        """(full reference-order traversals, restricted second passes) of the closest-point probes on this scene"""
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        check(_lib.load().wost_scene_traversal_stats(self.h, ctypes.byref(a), ctypes.byref(b), 1 if reset else 0))
+        return a.value, b.value
+
     def nearest(self, pts):
         pts = np.ascontiguousarray(pts, np.float32).reshape(-1, self.dim)
         idx = np.zeros(len(pts), np.uint32)
@@ -290,6 +296,12 @@ class _Integrator:
         out = np.zeros((self.settings.frame_h, self.settings.frame_w, 3), np.float32)
         check(_lib.load().wost_film_stderr(self.h, _p(out)))
         return out
+
+    def traversal_stats(self, reset=True):
+        """(full reference-order traversals, restricted second passes) of this integrator's closest-point queries"""
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        check(_lib.load().wost_traversal_stats(self.h, ctypes.byref(a), ctypes.byref(b), 1 if reset else 0))
+        return a.value, b.value
 
     def film_device_ptr(self, channel=CH_SOLUTION):
         p = c_void_p()

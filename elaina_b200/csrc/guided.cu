@@ -118,7 +118,7 @@ namespace wost
         float R_D = dm_inf();
         uint32_t pos = kInvalid;
         if (c.dir.nprims > 0)
-            query_nearest_sync<D, false>(c.dir, it.w.x, st, pos, R_D, valid);
+            query_nearest_sync<D, false>(c.dir, it.w.x, st, pos, R_D, valid, c.eps);
         if (!valid)
             return false;
         PixelAccT<true> acc;
@@ -271,13 +271,16 @@ namespace wost
                                 // the bounce moved the walk by R_B * dir from a point whose closest distance was R_D; without a
                                 // Neumann mesh R_B = max(1e-4, R_D) >= R_D, so d(x') <= 2 R_B (triangle inequality + rounding slack)
                                 const float bound = c.neu.nprims == 0 ? it.R_B * 2.0002f : dm_inf();
-                                trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, bound);
+                                trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, bound, c.eps, (F & kFeatNeumann) != 0);
                             }
                         }
                         else
                             exhausted = true;
                     }
                 }
+                // walks ~1e8 units away from the scene: the warp scans the leaves together (lbvh.cuh, phase 4)
+                if (D == 2 && (F & kFeatNeumann) && (nearest_brute_warp<D>(c.dir, it.w.x, trav && t.phase == 4, t) >> lane & 1u))
+                    trav = false;
             }
             else if (trav_mask == 0u)
                 break;
@@ -510,7 +513,7 @@ namespace wost
                         // bound: distance to the primitive that was closest a step ago when this lane knows it, else R_D + |step|
                         const float bound = (win_known && t.win != kInvalid) ? prim_distance(load_prim(c.dir.leaf_prim + t.win), it.w.x) * 1.00001f
                                                                              : (rd + vlen(vsub(it.w.x, x0))) * 1.00001f;
-                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, bound);
+                        trav = nearest_begin<D, false>(c.dir, it.w.x, st, t, bound, c.eps, (F & kFeatNeumann) != 0);
                     }
                     else
                     {
@@ -518,6 +521,8 @@ namespace wost
                         has = false;
                     }
                 }
+                if (D == 2 && (F & kFeatNeumann) && (nearest_brute_warp<D>(c.dir, it.w.x, trav && t.phase == 4, t) >> lane & 1u))
+                    trav = false;
             }
             else if (trav_mask == 0u)
                 break;

@@ -179,7 +179,10 @@ namespace wost
 
     // resident CTAs per SM the lean 3D variants are compiled for (64 registers: a few spilled bytes buy an eighth CTA; c4 +8%);
     // 0 = no request, the compiler's own budget (an explicit request cost the 2D kernels 2-7%)
-    constexpr int persist_min_ctas(int D, bool ref_order, int F) { return (D == 3 && !ref_order && !(F & kFeatNeumann)) ? 8 : 0; }
+    constexpr int persist_min_ctas(int D, bool ref_order, int F)
+    {
+        return ((D == 3 && !ref_order && !(F & kFeatNeumann)) || (D == 2 && !ref_order && F == kFeatNeumann)) ? 8 : 0;
+    }
     template <int D, bool RefOrder, int F>
     __global__ void __launch_bounds__(kWalkBlock, persist_min_ctas(D, RefOrder, F)) k_walk_persistent(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ PersistArgs a)
     {
@@ -200,10 +203,29 @@ namespace wost
         for (int k = 0; k < D; ++k)
             w.x[k] = w.nN[k] = 0.0f;
         t.win = kInvalid, t.best = 0.0f;
+#ifdef WOST_TRAV_DEBUG
+        t.dbg_dec = 0;
+        long long dbg_t0 = clock64();
+        unsigned long long *dbg_cyc = reinterpret_cast<unsigned long long *>(a.overflow + 32); // [0..7] trip-iteration cycles, [8..15] tail-iteration cycles per decade
+#endif
         for (;;)
         {
             const unsigned trav_mask = __ballot_sync(kFullMask, trav);
             const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has_walk || !exhausted));
+#ifdef WOST_TRAV_DEBUG
+            {
+                // attribute the previous iteration of this warp to the farthest query decade among its lanes
+                int dec = (trav || has_walk) ? (t.dbg_dec & 7) : 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+                    dec = max(dec, __shfl_xor_sync(kFullMask, dec, o));
+                const long long now = clock64();
+                const bool tail_iter = pend_mask != 0u && (__popc(pend_mask) >= a.refill_threshold || trav_mask == 0u);
+                if (lane == 0)
+                    atomicAdd(dbg_cyc + (tail_iter ? 8 : 0) + dec, (unsigned long long)(now - dbg_t0));
+                dbg_t0 = now;
+            }
+#endif
             if (pend_mask != 0u && (__popc(pend_mask) >= a.refill_threshold || trav_mask == 0u))
             {
                 if (!trav && has_walk)
@@ -269,8 +291,12 @@ namespace wost
                     if (fresh)
                         fresh = false; // result already in t: the lane stays pending and takes the next tail phase
                     else
-                        trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t, bound);
+                        trav = nearest_begin<D, RefOrder>(c.dir, w.x, st, t, bound, c.eps, (F & kFeatNeumann) != 0);
                 }
+                // walks that are ~1e8 units away from the scene: the warp scans the leaves together (lbvh.cuh, phase 4)
+                // (only in the variants with a Neumann mesh: walks leave a scene through the corners of closed Neumann polygons)
+                if (!RefOrder && D == 2 && (F & kFeatNeumann) && (nearest_brute_warp<D>(c.dir, w.x, trav && t.phase == 4, t) >> lane & 1u))
+                    trav = false;
             }
             else if (trav_mask == 0u)
                 break;
@@ -813,7 +839,7 @@ extern "C"
         if (kind == WOST_GUIDED && (it->d_cursor64.alloc(1) != cudaSuccess || guided_alloc(it) != WOST_OK))
             return fail("guided buffer allocation");
         if (it->d_counts.alloc((size_t)3 * (s.max_walking_depth + 2)) != cudaSuccess || it->d_steps.alloc(1) != cudaSuccess ||
-            it->d_acc.alloc((size_t)S * std::max(1, it->n_active)) != cudaSuccess || it->d_overflow.alloc(1) != cudaSuccess)
+            it->d_acc.alloc((size_t)S * std::max(1, it->n_active)) != cudaSuccess || it->d_overflow.alloc(96) != cudaSuccess)
             return fail("buffer allocation");
         for (int c = 0; c < WOST_CH_COUNT; ++c)
         {
@@ -824,7 +850,7 @@ extern "C"
             else
                 cudaMemset(it->film[c].ptr, 0, sizeof(float) * (size_t)it->npix * 5);
         }
-        cudaMemset(it->d_overflow.ptr, 0, sizeof(int));
+        cudaMemset(it->d_overflow.ptr, 0, 96 * sizeof(int));
         if (cudaStreamCreateWithFlags(&it->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&it->ev0) != cudaSuccess ||
             cudaEventCreate(&it->ev1) != cudaSuccess)
             return fail("stream/event creation");
@@ -954,6 +980,32 @@ extern "C"
         if (!it || !d_ptr || channel < 0 || channel >= WOST_CH_COUNT)
             return WOST_ERR_INVALID;
         *d_ptr = it->film[channel].ptr;
+        return WOST_OK;
+    }
+    wost_status wost_traversal_stats(wost_integrator *it, uint64_t *full_reference_order, uint64_t *restricted_second_pass, int reset)
+    {
+        if (!it)
+            return WOST_ERR_INVALID;
+        int h[4] = {0, 0, 0, 0};
+        WOST_CUDA_TRY(cudaMemcpyAsync(h, it->d_overflow.ptr, sizeof(h), cudaMemcpyDeviceToHost, it->stream));
+        WOST_CUDA_TRY(cudaStreamSynchronize(it->stream));
+        if (full_reference_order)
+            *full_reference_order = (uint64_t)(unsigned)h[1];
+        if (restricted_second_pass)
+            *restricted_second_pass = (uint64_t)(unsigned)h[2];
+        if (reset)
+            WOST_CUDA_TRY(cudaMemsetAsync(it->d_overflow.ptr + 1, 0, 2 * sizeof(int), it->stream));
+        return WOST_OK;
+    }
+    // diagnostics (library built with -DWOST_TRAV_DEBUG): closest-point trips [0..7] and queries [8..15] per decade of max |coordinate|
+    wost_status wost_debug_counters(wost_integrator *it, unsigned int *out16)
+    {
+        if (!it || !out16)
+            return WOST_ERR_INVALID;
+        // out: [0..15] trip / query counts, [16..47] 16 x 64-bit warp-cycle sums (trip iterations, tail iterations) per decade
+        WOST_CUDA_TRY(cudaMemcpy(out16, it->d_overflow.ptr + 8, 16 * sizeof(int), cudaMemcpyDeviceToHost));
+        WOST_CUDA_TRY(cudaMemcpy(out16 + 16, it->d_overflow.ptr + 32, 32 * sizeof(int), cudaMemcpyDeviceToHost));
+        WOST_CUDA_TRY(cudaMemset(it->d_overflow.ptr + 8, 0, 88 * sizeof(int)));
         return WOST_OK;
     }
     wost_status wost_last_launch_count(wost_integrator *it, uint64_t *kernel_launches)

@@ -245,7 +245,7 @@ namespace wost
         uint2 *base; // column of this thread (already offset by tid)
         int stride;  // blockDim.x
         int sp;
-        int *overflow;
+        int *overflow; // [0] stack overflow flag, [1] full reference-order traversals, [2] restricted second passes (statistics)
         uint2 *spill; // kSpillLevels entries of thread-local memory owned by the kernel (kept outside this struct so that the
                       // struct itself -- sp, base -- stays in registers)
         WOST_DEV void init(uint2 *smem, int *overflow_flag, uint2 *spill_mem)
@@ -321,8 +321,10 @@ namespace wost
     //     the re-squared best and drops tied / 1-ulp-near minima depending on visit order. Whenever phase 0 saw more
     //     than one leaf within 8 ulp of the minimum, the lane continues in phase 1 restricted to thrW = the final
     //     pruning threshold: only the subtrees holding the (near-)tied minima are re-walked, in the reference's order.
-    //   * far field (|q| beyond ~1000x the mesh, where fp32 collapses all distances): phase 1 from the start.
+    //   * 2D far field (|q| > kFar2D, where the 1e-3 padding no longer dominates rounding): B200 order + near-tie count +
+    //     restricted pass, like 3D ("phase 2"). 3D far field (|q| beyond ~1000x the mesh): phase 1 from the start.
     constexpr uint32_t kFullMask = 0xffffffffu;
+    constexpr float kFar2D = 2000.0f; // 1e-3 (scene.cuh:12 bvh_offset) / (8 * 2^-24), rounded down: see nearest_begin
 
     template <int D>
     struct NearestTrav
@@ -337,6 +339,9 @@ namespace wost
         int n_near;     // 3D: leaves seen within 8 ulp of the running minimum
         int phase;
         bool have_rank;
+#ifdef WOST_TRAV_DEBUG
+        int dbg_dec; // decade of max |coordinate| of the query: trips are counted per decade in overflow[8 + dec] (16 + dec: queries)
+#endif
     };
 
     template <int D>
@@ -350,12 +355,104 @@ namespace wost
         t.cur_d = box_mindist(root_box_of(bvh), q);
         st.sp = 0;
     }
+    // 2D far field (see nearest_begin): phase 2 = count near-ties, finish with the restricted pass; phase 3 = distance only
+    template <int D>
+    __device__ __noinline__ int nearest_far_phase(const float *root_box, Vec<D> q, float slack, float need_index_below, bool allow_brute)
+    {
+        Box<D> r;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+        {
+            r.up[k] = root_box[k];
+            r.lo[k] = root_box[D + k];
+        }
+        const float lim = 2.0f * need_index_below + slack;
+        if (!(box_mindist(r, q) > lim * lim)) // never true when need_index_below is inf
+            return 2;
+        // ultra-far (|q| > ~2^17 x the mesh extent, ~1e8 for a 600-unit scene): even the 2^-21 |q| shell of fp32-indistinguishable
+        // candidates covers most of the mesh, a traversal visits ~all nodes one dependent load at a time (13 000 trips measured
+        // on data/fille, and the handful of lanes that own such walks ran for seconds after every other warp had finished).
+        // Phase 4: the warp scans all leaves cooperatively instead (nearest_brute_warp).
+        float ext = 0.0f;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            ext = fmax_nn(ext, r.up[k] - r.lo[k]);
+        return (allow_brute && slack > ext) ? 4 : 3; // slack is 2^-19 |q| here: the 2^-21 |q| shell is thicker than a quarter of the mesh
+    }
+    // Phase 4 (distance-only, ultra-far): all 32 lanes evaluate the leaves of the lanes that asked (`mine`), 32 leaves per
+    // step, coalesced, no dependent loads; result = exact minimum of the re-squared fp32 leaf distances (lowest leaf position
+    // among equals). Warp-synchronous: every lane of the warp calls it. Returns the lanes that were served.
+    template <int D>
+    __device__ __noinline__ uint2 nearest_brute_scan(const DevBVH<D> *bvh, Vec<D> q, unsigned served) // rare: out of line
+    {
+        const int lane = threadIdx.x & 31;
+        uint2 mine_r = make_uint2(kInvalid, __float_as_uint(dm_inf()));
+        for (unsigned m = served; m != 0u; m &= m - 1u)
+        {
+            const int src = __ffs(m) - 1;
+            Vec<D> qs;
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+                qs[k] = __shfl_sync(kFullMask, q[k], src);
+            float best = dm_inf();
+            uint32_t win = kInvalid;
+            for (uint32_t pos = (uint32_t)lane; pos < (uint32_t)bvh->nprims; pos += 32u)
+            {
+                const float d = dm_sqrt(prim_distance_d2(load_prim(bvh->leaf_prim + pos), qs));
+                const float g = d * d;
+                if (g < best)
+                {
+                    best = g;
+                    win = pos;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1)
+            {
+                const float ob = __shfl_xor_sync(kFullMask, best, o);
+                const uint32_t ow = __shfl_xor_sync(kFullMask, win, o);
+                if (ob < best || (ob == best && ow < win))
+                {
+                    best = ob;
+                    win = ow;
+                }
+            }
+            if (lane == src)
+                mine_r = make_uint2(win, __float_as_uint(best));
+        }
+        return mine_r;
+    }
+    template <int D>
+    WOST_DEV unsigned nearest_brute_warp(const DevBVH<D> &bvh, const Vec<D> &q, bool mine, NearestTrav<D> &t)
+    {
+        const unsigned served = __ballot_sync(kFullMask, mine);
+        if (__builtin_expect(served != 0u, 0))
+        {
+            const uint2 r = nearest_brute_scan<D>(&bvh, q, served);
+            if (mine)
+            {
+                t.win = r.x;
+                t.best = __uint_as_float(r.y);
+            }
+        }
+        return served;
+    }
     // -> true when trips are needed; false when the result is already in t (0 or 1 primitives)
     // bound: an a-priori upper bound of the result (inf when unknown). A walk that moved by s from a point whose
     // closest distance was R knows d(x') <= R + s; seeding the pruning threshold with it keeps the far siblings of the
     // first descent off the stack (they are otherwise pushed, and popped later only to be discarded).
+    // need_index_below: the caller only uses the winner's INDEX when the distance is below this value (the walker: the
+    // epsilon shell, uniform/integrator.cu:155-183; the probes: always -> inf). 2D far-field queries that provably end
+    // above it (twice the value away from the root box) run in "distance-only" mode (phase 3): no near-tie bookkeeping, no
+    // second pass, and a pruning slack of 2^-21 |q| that only has to cover the rounding mismatch between a box distance and a
+    // leaf distance. The distance is then the exact minimum of the fp32 leaf distances over the reference's candidate set;
+    // the reference's own pick in that regime depends on its visit order by a few ulp (its pop-time test misprunes once the
+    // 1e-3 padding is below rounding), so this is a documented deviation for walks that have LEFT the scene by > 2000 units
+    // (DESIGN.md section 5). Without it such walks -- the reference leaks them through the corners of closed Neumann
+    // polygons -- cost a full traversal of every leaf per step.
     template <int D, bool RefOrder>
-    WOST_DEV bool nearest_begin(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t, float bound = dm_inf())
+    WOST_DEV bool nearest_begin(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t, float bound = dm_inf(),
+                                float need_index_below = dm_inf(), bool allow_brute = false)
     {
         t.win = kInvalid;
         t.best = dm_inf();
@@ -378,12 +475,33 @@ namespace wost
 #pragma unroll
         for (int k = 0; k < D; ++k)
             qmax = fmax_nn(qmax, dm_abs(q[k]));
-        if (qmax > 1024.0f * bvh.max_abs_coord || (D == 2 && qmax > 2000.0f))
+        if (D == 3 && qmax > 1024.0f * bvh.max_abs_coord)
         {
+            if (st.overflow)
+                atomicAdd(st.overflow + 1, 1); // statistics: full traversals in the reference's order
             nearest_enter_phase1(bvh, q, st, t, dm_inf());
             return true;
         }
+        // 2D: the "no second pass" argument above needs the reference's box padding (1e-3) to dominate the rounding of a
+        // distance, d * 2^-24 * 8 < 1e-3, i.e. coordinates below kFar2D = 1e-3 / (8 * 2^-24) ~ 2097. Beyond it (large scenes,
+        // walks that left the domain) the query still runs in the B200 order, but counts near-ties like the 3D path (phase 2)
+        // and finishes with the restricted reference-order pass when there was more than one: the cost then grows smoothly
+        // with the distance (the pass covers the subtrees within 2^-19 |q| of the minimum) instead of jumping to a full
+        // traversal of every leaf. (Round 1 switched to the full reference-order traversal at |q| > 2000: walks that leak
+        // through a corner of a closed Neumann square -- the reference's walks do, tests/test_oracle_b1_pin.py -- and wander
+        // off to 1e3..1e8 made data/fille 9x slower per walk-step than data/ladybug.)
+#ifdef WOST_TRAV_DEBUG
+        t.dbg_dec = qmax < 600.0f ? 0 : (qmax < 2000.0f ? 1 : (qmax < 1e4f ? 2 : (qmax < 1e5f ? 3 : (qmax < 1e6f ? 4 : (qmax < 1e7f ? 5 : (qmax < 1e8f ? 6 : 7))))));
+        if (st.overflow)
+            atomicAdd(st.overflow + 16 + t.dbg_dec, 1);
+#endif
         t.slack = fmax_nn(qmax, bvh.max_abs_coord) * 1.9073486328125e-06f; // 2^-19
+        if (D == 2 && __builtin_expect(qmax > kFar2D, 0))
+        {
+            t.phase = nearest_far_phase<D>(bvh.root_box, q, t.slack, need_index_below, allow_brute); // rare: out of line (registers of the hot loop)
+            if (t.phase >= 3)
+                t.slack *= 0.25f; // 2^-21 |q|
+        }
         {
             const float u = bound + t.slack; // inf stays inf
             t.thr = u * u;
@@ -467,7 +585,7 @@ namespace wost
             const float d = dm_sqrt(d2);
             const float g = d * d;
             bool take = g < t.best;
-            if (D == 3)
+            if (D == 3 || t.phase == 2)
             {
                 if (take)
                     t.n_near = (t.best <= g * 1.000001f) ? t.n_near + 1 : 1;
@@ -505,6 +623,10 @@ namespace wost
     template <int D, bool RefOrder>
     WOST_DEV bool nearest_trip(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, NearestTrav<D> &t)
     {
+#ifdef WOST_TRAV_DEBUG
+        if (st.overflow)
+            atomicAdd(st.overflow + 8 + t.dbg_dec, 1);
+#endif
         if (RefOrder || __builtin_expect(t.phase == 1, 0)) // phase 1: far field / 3D tie resolution, kept off the hot path
             return nearest_trip_ref<D, RefOrder>(bvh, q, st, t);
         bool have = false;
@@ -585,8 +707,10 @@ namespace wost
                 return true;
             }
         }
-        if (D == 3 && __builtin_expect(t.n_near > 1, 0))
+        if ((D == 3 || t.phase == 2) && __builtin_expect(t.n_near > 1, 0))
         {
+            if (st.overflow)
+                atomicAdd(st.overflow + 2, 1); // statistics: restricted second passes
             nearest_enter_phase1(bvh, q, st, t, t.thr);
             return true;
         }
@@ -596,12 +720,15 @@ namespace wost
     // Warp-synchronous drivers: the 32 lanes of a warp call these together; lanes without a query pass valid = false.
     // Returns the LEAF POSITION of the winner (original index = leaf_obj[pos]) and the distance.
     template <int D, bool RefOrder>
-    WOST_DEV void query_nearest_sync(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid)
+    WOST_DEV void query_nearest_sync(const DevBVH<D> &bvh, const Vec<D> &q, SmemStack &st, uint32_t &leaf_pos, float &dist, bool valid,
+                                     float need_index_below = dm_inf())
     {
         NearestTrav<D> t;
         bool active = false;
         if (valid)
-            active = nearest_begin<D, RefOrder>(bvh, q, st, t);
+            active = nearest_begin<D, RefOrder>(bvh, q, st, t, dm_inf(), need_index_below, true);
+        if (!RefOrder && D == 2 && (nearest_brute_warp<D>(bvh, q, active && t.phase == 4, t) >> (threadIdx.x & 31) & 1u))
+            active = false;
         while (__any_sync(kFullMask, active))
         {
             if (active)

@@ -1058,8 +1058,8 @@ namespace wost
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_box, s->d_boxes.ptr, sizeof(float) * 2 * D, cudaMemcpyDeviceToHost, st));
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_cone, s->d_cones.ptr, sizeof(float) * (D + 2), cudaMemcpyDeviceToHost, st));
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_ext, ext.ptr, sizeof(float) * 2 * D, cudaMemcpyDeviceToHost, st));
-        WOST_CUDA_TRY(s->d_overflow.alloc(1));
-        WOST_CUDA_TRY(cudaMemsetAsync(s->d_overflow.ptr, 0, sizeof(int), st));
+        WOST_CUDA_TRY(s->d_overflow.alloc(32));
+        WOST_CUDA_TRY(cudaMemsetAsync(s->d_overflow.ptr, 0, 32 * sizeof(int), st));
         WOST_CUDA_TRY(cudaStreamSynchronize(st));
         WOST_CUDA_TRY(cudaGetLastError());
         return WOST_OK;
@@ -1161,6 +1161,18 @@ namespace wost
         const int blocks = div_up(n, kQueryBlock);
         const int cap = sm_count() * 8;
         return std::max(1, std::min(blocks, cap));
+    }
+    wost_status scene_traversal_stats(const wost_scene *s, uint64_t *full, uint64_t *restricted, int reset)
+    {
+        int h[4] = {0, 0, 0, 0};
+        WOST_CUDA_TRY(cudaMemcpy(h, s->d_overflow.ptr, sizeof(h), cudaMemcpyDeviceToHost));
+        if (full)
+            *full = (uint64_t)(unsigned)h[1];
+        if (restricted)
+            *restricted = (uint64_t)(unsigned)h[2];
+        if (reset)
+            WOST_CUDA_TRY(cudaMemset(s->d_overflow.ptr + 1, 0, 2 * sizeof(int)));
+        return WOST_OK;
     }
     static wost_status check_overflow(const wost_scene *s)
     {
@@ -1292,6 +1304,12 @@ extern "C"
         if (cones)
             WOST_CUDA_TRY(cudaMemcpy(cones, s->d_cones.ptr, NN * (s->dim + 2) * sizeof(float), cudaMemcpyDeviceToHost));
         return WOST_OK;
+    }
+    wost_status wost_scene_traversal_stats(const wost_scene *s, uint64_t *full_reference_order, uint64_t *restricted_second_pass, int reset)
+    {
+        if (!s)
+            return WOST_ERR_INVALID;
+        return scene_traversal_stats(s, full_reference_order, restricted_second_pass, reset);
     }
     wost_status wost_scene_dump_sorted(const wost_scene *s, uint32_t *morton, uint32_t *object_idx)
     {

@@ -550,7 +550,7 @@ namespace wost
         float R_D = dm_inf();
         uint32_t pos = kInvalid;
         if (c.dir.nprims > 0)
-            query_nearest_sync<D, RefOrder>(c.dir, w.x, st, pos, R_D, valid);
+            query_nearest_sync<D, RefOrder>(c.dir, w.x, st, pos, R_D, valid, c.eps);
         if (!valid)
             return false;
         return walk_step_tail<D>(c, w, depth, st, acc, R_D, pos);

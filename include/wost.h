@@ -48,6 +48,11 @@ extern "C"
      * nodes num_nodes*4 u32 (parent,left,right,object), aabbs num_nodes*2*dim (upper,lower), cones num_nodes*(dim+2) */
     wost_status wost_scene_dump_bvh(const wost_scene *scene, uint32_t *nodes, float *aabbs, float *cones);
     wost_status wost_scene_dump_sorted(const wost_scene *scene, uint32_t *morton, uint32_t *object_idx);
+    /* Closest-point traversal statistics of the parity probes on this scene since the last reset: queries that ran a FULL
+     * traversal in the reference's visit order (3D far field only) and queries that finished with the restricted
+     * reference-order second pass (near-ties in 3D, and in 2D beyond |q| ~ 2000 where the reference's 1e-3 box padding no
+     * longer dominates rounding; core/query.cuh:238-318). Everything else ran the B200 order alone. */
+    wost_status wost_scene_traversal_stats(const wost_scene *scene, uint64_t *full_reference_order, uint64_t *restricted_second_pass, int reset);
 
     /* lbvh::query_device(bvh, nearest(q), distance_calculator) -- core/query.cuh:238-318.
      * Host buffers; pts n*dim. idx = closest primitive, dist = distance (the star-radius input R_D). */
@@ -174,6 +179,11 @@ extern "C"
     wost_status wost_film_stderr(wost_integrator *it, float *out_se_rgb);
     /* device pointer of the film of `channel` (W*H*5 floats) for NCCL gathers issued by the host language */
     wost_status wost_film_device_ptr(wost_integrator *it, int channel, void **d_ptr);
+    /* the same statistics for the closest-point queries of this integrator's solves and channel renders */
+    wost_status wost_traversal_stats(wost_integrator *it, uint64_t *full_reference_order, uint64_t *restricted_second_pass, int reset);
+    /* diagnostics, meaningful only when the library was built with -DWOST_TRAV_DEBUG: closest-point trips [0..7] and queries
+     * [8..15] of this integrator per decade of the query's max |coordinate| (<600, <2e3, <1e4, ..., >=1e8); read and reset */
+    wost_status wost_debug_counters(wost_integrator *it, unsigned int *out16);
     /* counters of the last solve */
     wost_status wost_last_launch_count(wost_integrator *it, uint64_t *kernel_launches);
     /* launches of the fused walk-step kernel in the last solve and their summed device time (CUDA events on the

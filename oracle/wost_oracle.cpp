@@ -22,6 +22,8 @@ namespace
     int g_math_mode = 0;
     // uniform walker draws: 0 = Philox (product), 1 = the reference's per-pixel PCG32 (wost_oracle_walk.inl)
     int g_rng_mode = 0;
+    uint32_t *g_pixel_steps = nullptr; // diagnostics (orc_set_pixel_steps)
+    float *g_trace = nullptr;          // diagnostics (orc_set_trace)
     inline float m_acos(float x) { return g_math_mode ? acosf(x) : dm_acos(x); }
     inline float m_asin(float x) { return g_math_mode ? asinf(x) : dm_asin(x); }
     inline float m_atan2(float y, float x) { return g_math_mode ? atan2f(y, x) : dm_atan2(y, x); }

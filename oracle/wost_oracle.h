@@ -26,6 +26,8 @@ extern "C"
      * consumption order (core/sampler.h:10-103, integrator/uniform/integrator.cu:72-77), to compare orc_solve_uniform
      * field-for-field with the reference's own CUDA build (tests/golden/b1_*.npz) */
     void orc_set_rng_mode(int mode);
+    void orc_set_pixel_steps(uint32_t *buf); /* diagnostics: per-pixel walk-steps of orc_solve_uniform (W*H uint32), NULL = off */
+    void orc_set_trace(float *buf); /* diagnostics: walk positions [depth][dim] of a single-pixel, 1-spp, 1-thread solve */
     void orc_pcg32_probe(uint64_t initstate, uint64_t initseq, int64_t delta, int n, uint32_t *out); /* PCG32 known answers */
 
     /* ---- geometry ---- */

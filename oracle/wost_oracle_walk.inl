@@ -421,6 +421,9 @@ namespace
             {
                 ++steps;
                 dr.depth = (uint32_t)depth;
+                if (g_trace) // diagnostics: positions of the walk (single-threaded use)
+                    for (int k = 0; k < D; ++k)
+                        g_trace[(size_t)depth * D + k] = x[k];
                 // ---- separate (integrator.cu:102-212)
                 float R_D = INF_F;
                 if (sd)
@@ -628,11 +631,17 @@ extern "C"
                 walk_pixel<2>(P, *s, P.dir ? P.dir->s2 : nullptr, P.neu ? P.neu->s2 : nullptr, pixel, sol, st);
             else
                 walk_pixel<3>(P, *s, P.dir ? P.dir->s3 : nullptr, P.neu ? P.neu->s3 : nullptr, pixel, sol, st);
+            if (g_pixel_steps)
+                g_pixel_steps[pixel] = (uint32_t)st;
             total.fetch_add(st, std::memory_order_relaxed); });
         if (steps)
             *steps = total.load();
     }
 
+    // diagnostics: when set, orc_solve_uniform also writes the walk-steps of every pixel it evaluates (W*H uint32)
+    void orc_set_pixel_steps(uint32_t *buf) { g_pixel_steps = buf; }
+    // diagnostics: when set, every walk writes its positions [depth][dim] here (call orc_solve_uniform on ONE pixel, 1 spp, 1 thread)
+    void orc_set_trace(float *buf) { g_trace = buf; }
     // known-answer probe: setSeed(initstate, initseq), advance(delta), then n raw 32-bit outputs
     void orc_pcg32_probe(uint64_t initstate, uint64_t initseq, int64_t delta, int n, uint32_t *out)
     {

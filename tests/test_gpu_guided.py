@@ -265,14 +265,17 @@ def test_guided_training_learns_and_stays_unbiased():
     g = 2.0 * np.arange(W, dtype=np.float32) / W - 1.0
     X, Y = np.meshgrid(0.6 * g, 0.6 * g)
     ref = scenes.harmonic_2d(np.stack([X, Y], -1), 3)
+    # the corners of the frame lie outside the star-shaped curve (exterior problem, different solution): interior pixels only
+    inside = np.hypot(X, Y) < 1.0 + 0.3 * np.sin(5.0 * np.arctan2(Y, X)) - 0.02
+    assert inside.mean() > 0.9
     err = sol - ref
     se = it.film_stderr()[..., 0]                      # measured: one accumulator slot per sample (spp_batch == spp)
-    z = err / np.maximum(se, 1e-9)
-    assert np.mean(np.abs(z) <= 3.0) >= 0.99, float(np.mean(np.abs(z) <= 3.0))   # nominal 99.7 %, 4096 pixels
+    z = (err / np.maximum(se, 1e-9))[inside]
+    assert np.mean(np.abs(z) <= 3.0) >= 0.985, float(np.mean(np.abs(z) <= 3.0))  # nominal 99.7 %; 96 samples of a skewed distribution
     assert 0.6 <= np.mean(np.abs(z) <= 1.0) <= 0.78                           # calibrated errors: ~68 % within one
     assert abs(z.mean()) < 0.2
-    relmse = np.mean(err ** 2 / (ref ** 2 + 1e-2))
-    assert relmse < 1.3 * np.mean(se ** 2 / (ref ** 2 + 1e-2))
+    relmse = np.mean((err ** 2 / (ref ** 2 + 1e-2))[inside])
+    assert relmse < 1.3 * np.mean((se ** 2 / (ref ** 2 + 1e-2))[inside])
 
 
 def test_guided_training_samples_match_oracle(oracle):

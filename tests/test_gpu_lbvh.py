@@ -50,12 +50,18 @@ def _scene_cases():
     tidx = rng.randint(0, 2000, (3000, 3)).astype(np.int32)
     tidx = tidx[(tidx[:, 0] != tidx[:, 1]) & (tidx[:, 1] != tidx[:, 2]) & (tidx[:, 0] != tidx[:, 2])]
     cases["soup3d_random"] = (3, tri, tidx)
+    from elaina_b200 import workloads
+    for shipped in ("ladybug", "fille"):   # BASELINE configs[0]/[1] on their REAL geometry: 61 476 / 66 367 segments, 64-bit Morton path
+        dv, dp, _, _ = workloads._shipped(shipped)
+        cases[shipped] = (2, dv, dp)
+    sv, sp = scenes.star_polygon(3000)
+    cases["star_x4096"] = (2, (sv * np.float32(4096.0) + np.float32(30000.0)).astype(np.float32), sp)  # a scene authored on a large canvas
     cases["single_segment"] = (2, np.array([[0, 0], [1, 0.5]], np.float32), np.array([[0, 1]], np.int32))
     cases["two_triangles"] = (3, np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 1, 0.3]], np.float32), np.array([[0, 1, 2], [1, 3, 2]], np.int32))
     return cases
 
 
-@pytest.mark.parametrize("name", ["star10k", "ico5", "soup2d_random", "soup3d_random", "single_segment", "two_triangles"])
+@pytest.mark.parametrize("name", ["star10k", "ico5", "soup2d_random", "soup3d_random", "single_segment", "two_triangles", "ladybug", "fille", "star_x4096"])
 def test_gpu_matches_oracle_bit_exact(oracle, name):
     """Build order, topology, boxes AND cones bit-exact (one arithmetic), all five query kinds bit-exact."""
     api = _api()
@@ -143,6 +149,46 @@ def test_nearest_tie_breaks_and_far_queries(oracle, name):
         ig, dg = sg.nearest(q)
         assert np.array_equal(io, ig)
         assert np.array_equal(bits(do), bits(dg))
+
+
+def test_survey_model_obj_rows_on_gpu():
+    """SURVEY.md section 8(c), data/ladybug/model.obj rows (values from the host-compiled reference LBVH)."""
+    api = _api()
+    from elaina_b200 import workloads
+    dv, dp, _, _ = workloads._shipped("ladybug")
+    s = api.Scene(2, dv, dp)
+    assert s.num_nodes == 122951 and s.used_morton64
+    q = np.array([(100, 250), (180, 220), (260, 190), (340, 160), (420, 130)], np.float32)
+    idx, dist = s.nearest(q)
+    assert idx.tolist() == [338, 44560, 18206, 39513, 58322]
+    np.testing.assert_array_equal(dist, np.array([1.48958969, 2.60965014, 18.6593742, 5.0058713, 1.48767483], np.float32))
+    np.testing.assert_array_equal(s.silhouette(q), np.array([14.9877558, 4.2426405, 19.1049728, 14.5602198, 2.23606801], np.float32))
+    hit, t, uv, obj = s.ray(q, np.tile(np.array([0.6, 0.8], np.float32), (5, 1)), np.full(5, 1e9, np.float32))
+    assert hit.tolist() == [1] * 5 and obj.tolist() == [9655, 44578, 5780, 37537, 56845]
+    np.testing.assert_array_equal(t, np.array([10.078681, 3.18717504, 260.930939, 18.5931568, 57.7269135], np.float32))
+
+
+def test_large_canvas_scene_stays_on_the_fast_path(oracle):
+    """round 1 sent every 2D query with |coordinate| > 2000 to a full traversal in the reference's visit
+    order. A scene authored on a 4096-unit canvas (coordinates 25 000-35 000) must be answered by the B200 order -- at most a
+    restricted second pass for near-ties -- and still bit-exactly."""
+    api = _api()
+    dim, v, p = _scene_cases()["star_x4096"]
+    so, sg = oracle.scene(dim, v, p), api.Scene(dim, v, p)
+    rng = np.random.RandomState(3)
+    q = (30000.0 + (rng.rand(20000, 2) * 2 - 1) * 6000.0).astype(np.float32)
+    on_vertex = v[rng.randint(0, len(v), 2000)]
+    sg.traversal_stats(reset=True)
+    for pts in (q, on_vertex):
+        io, do = so.nearest(pts)
+        ig, dg = sg.nearest(pts)
+        assert np.array_equal(io, ig) and np.array_equal(bits(do), bits(dg))
+    full, restricted = sg.traversal_stats()
+    assert full == 0
+    # queries whose closest point is a polygon VERTEX tie exactly between its two segments and take the restricted second pass
+    # (the subtree around that vertex, in the reference's order): about 44 % of the queries around this smooth polygon
+    assert restricted < 0.6 * (len(q) + len(on_vertex)), restricted
+    print("restricted second passes: %d of %d queries" % (restricted, len(q) + len(on_vertex)))
 
 
 @pytest.mark.gpu

@@ -101,15 +101,18 @@ def test_uniform_matches_analytic_harmonic_2d():
     g = 2.0 * np.arange(W, dtype=np.float32) / W - 1.0
     X, Y = np.meshgrid(0.6 * g, 0.6 * g)
     ref = scenes.harmonic_2d(np.stack([X, Y], -1), 3)
+    # the corners of the frame lie outside the star-shaped curve (exterior problem, different solution): interior pixels only
+    inside = np.hypot(X, Y) < 1.0 + 0.3 * np.sin(5.0 * np.arctan2(Y, X)) - 0.02
+    assert inside.mean() > 0.9
     err = sol - ref
     # measured per-pixel standard error (wost_film_stderr; spp_batch == spp -> one slot per sample, exact sample variance)
     se = it.film_stderr()[..., 0]
-    z = err / np.maximum(se, 1e-9)
-    assert np.mean(np.abs(z) <= 3.0) >= 0.995, float(np.mean(np.abs(z) <= 3.0))  # nominal 99.7 % over 4096 pixels (count s.d. 0.08 %)
+    z = (err / np.maximum(se, 1e-9))[inside]
+    assert np.mean(np.abs(z) <= 3.0) >= 0.99, float(np.mean(np.abs(z) <= 3.0))  # nominal 99.7 %; skewed per-walk distribution at 256 samples
     assert 0.64 <= np.mean(np.abs(z) <= 1.0) <= 0.72
     assert abs(z.mean()) < 0.1
-    relmse = np.mean(err ** 2 / (ref ** 2 + 1e-2))
-    expected = np.mean(se ** 2 / (ref ** 2 + 1e-2))   # what 256 spp can deliver on this problem: relMSE == mean relative variance
+    relmse = np.mean((err ** 2 / (ref ** 2 + 1e-2))[inside])
+    expected = np.mean((se ** 2 / (ref ** 2 + 1e-2))[inside])   # what 256 spp can deliver on this problem: relMSE == mean relative variance
     assert 0.8 * expected < relmse < 1.2 * expected, (relmse, expected)
     # the standard error does not depend on how samples are batched: 32 slots of 8 samples estimate the same quantity
     it2 = api.UniformIntegrator(prob, api.make_settings((W, W), 64, spp, 1e-3, seed=42, spp_batch=32))

@@ -70,6 +70,58 @@ def test_survey_golden_table(oracle):
     np.testing.assert_array_equal(t, np.array([425.0, 462.5, 500.0, 416.666656, 283.333313], np.float32))
 
 
+@pytest.mark.parametrize("mode", [1, 0])
+def test_survey_golden_table_model_obj(oracle, mode):
+    """the data/ladybug/model.obj rows (122 951 nodes, 61 476 objects, Morton collisions -> 64-bit keys)
+    on the shipped geometry (tests/golden/scene_ladybug.npz, the float32 vertices the reference's loader produces)."""
+    from elaina_b200 import workloads
+    dv, dp, _, _ = workloads._shipped("ladybug")
+    oracle.set_math_mode(mode)
+    try:
+        s = oracle.scene(2, dv, dp)
+        assert s.num_nodes == 122951 and len(dp) == 61476 and oracle.used_morton64(s)
+        q = np.array([(100, 250), (180, 220), (260, 190), (340, 160), (420, 130)], np.float32)
+        idx, dist = s.nearest(q)
+        assert idx.tolist() == [338, 44560, 18206, 39513, 58322]
+        np.testing.assert_array_equal(dist, np.array([1.48958969, 2.60965014, 18.6593742, 5.0058713, 1.48767483], np.float32))
+        np.testing.assert_array_equal(s.silhouette(q), np.array([14.9877558, 4.2426405, 19.1049728, 14.5602198, 2.23606801], np.float32))
+        hit, t, uv, obj = s.ray(q, np.tile(np.array([0.6, 0.8], np.float32), (5, 1)), np.full(5, 1e9, np.float32))
+        assert hit.tolist() == [1] * 5 and obj.tolist() == [9655, 44578, 5780, 37537, 56845]
+        np.testing.assert_array_equal(t, np.array([10.078681, 3.18717504, 260.930939, 18.5931568, 57.7269135], np.float32))
+    finally:
+        oracle.set_math_mode(0)
+
+
+@pytest.mark.parametrize("shipped", ["ladybug", "fille"])
+def test_oracle_equals_host_compiled_reference_on_shipped_geometry(oracle, shipped):
+    """the full tree and 5 000 queries of every kind on the real meshes of BASELINE configs[0]/[1], oracle (libm mode) vs the
+    reference's own headers compiled for the host (oracle/_ref; needs /root/reference at build time, so skipped on the GPU box
+    unless the prebuilt library travelled)"""
+    from oracle_lib import RefLBVH, have_ref
+    from helpers import random_queries
+    from elaina_b200 import workloads
+    if not have_ref():
+        pytest.skip("oracle/_ref/libref_lbvh.so not built")
+    dv, dp, _, _ = workloads._shipped(shipped)
+    oracle.set_math_mode(1)
+    try:
+        so, sr = oracle.scene(2, dv, dp), RefLBVH().scene(2, dv, dp)
+        no, ao, co = so.dump_bvh()
+        nr, ar, cr = sr.dump_bvh()
+        assert np.array_equal(no, nr) and np.array_equal(bits(ao), bits(ar))
+        q, d, md, u, rad = random_queries(dv, 5000, 4)
+        io, do = so.nearest(q)
+        ir, dr = sr.nearest(q)
+        assert np.array_equal(io, ir) and np.array_equal(bits(do), bits(dr))
+        for flip in (False, True):
+            assert np.array_equal(bits(so.silhouette(q, flip)), bits(sr.silhouette(q, flip)))
+        ho, to, uo, bo = so.ray(q, d, md)
+        hr, tr, ur, br = sr.ray(q, d, md)
+        assert np.array_equal(ho, hr) and np.array_equal(bo, br) and np.array_equal(bits(to), bits(tr))
+    finally:
+        oracle.set_math_mode(0)
+
+
 def test_detmath_accuracy(oracle):
     rng = np.random.RandomState(0)
     x = (rng.rand(200000).astype(np.float32) * 2 - 1) * 50
