@@ -86,6 +86,7 @@ SYMBOLS = [
     ("wost_scene_info", c_int, [c_void_p, _PP(c_int), _PP(c_int), _PP(c_int), _PP(c_int)]),
     ("wost_scene_dump_bvh", c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     ("wost_scene_dump_sorted", c_int, [c_void_p, c_void_p, c_void_p]),
+    ("wost_scene_dump_traversal_layout", c_int, [c_void_p, c_void_p, _PP(c_int), c_void_p]),
     ("wost_lbvh_nearest", c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     ("wost_lbvh_silhouette", c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
     ("wost_lbvh_ray", c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -107,8 +108,18 @@ SYMBOLS = [
     ("wost_scene_traversal_stats", c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     ("wost_film_device_ptr", c_int, [c_void_p, c_int, _PP(c_void_p)]),
     ("wost_last_launch_count", c_int, [c_void_p, _PP(c_u64)]),
+    ("wost_l2_window_bytes", c_int, [c_void_p, _PP(c_u64)]),
     ("wost_last_step_kernel_time", c_int, [c_void_p, _PP(c_u64), _PP(c_float)]),
     ("wost_run_config", c_int, [c_char_p]),
+    ("wost_comm_unique_id", c_int, [c_void_p]),
+    ("wost_comm_create", c_int, [c_int, c_int, c_void_p, _PP(c_void_p)]),
+    ("wost_comm_create_from_env", c_int, [_PP(c_void_p)]),
+    ("wost_comm_destroy", None, [c_void_p]),
+    ("wost_comm_info", c_int, [c_void_p, _PP(c_int), _PP(c_int), _PP(c_int)]),
+    ("wost_comm_shard_settings", c_int, [c_void_p, _PP(Settings), c_int]),
+    ("wost_integrator_set_comm", c_int, [c_void_p, c_void_p]),
+    ("wost_film_gather", c_int, [c_void_p, c_void_p, c_int, c_int]),
+    ("wost_comm_allreduce_f64", c_int, [c_void_p, c_void_p, c_int, c_int]),
     ("wost_reset_network", c_int, [c_void_p, c_char_p]),
     ("wost_reset_training", c_int, [c_void_p]),
     ("wost_query_network", c_int, [c_void_p, c_void_p, c_void_p]),

@@ -80,6 +80,16 @@ class Scene:
         check(_lib.load().wost_scene_dump_bvh(self.h, _p(nodes), _p(aabbs), _p(cones)))
         return nodes, aabbs, cones
 
+    def dump_traversal_layout(self):
+        """(records[num_prims-1, F], leaf_verts[num_prims, dim, dim]) of the B200 traversal layout (csrc/lbvh.cuh: TNode)"""
+        L = _lib.load()
+        nf = ctypes.c_int()
+        check(L.wost_scene_dump_traversal_layout(self.h, None, ctypes.byref(nf), None))
+        rec = np.zeros((max(0, self.num_prims - 1), nf.value), np.float32)
+        lv = np.zeros((self.num_prims, self.dim, self.dim), np.float32)
+        check(L.wost_scene_dump_traversal_layout(self.h, _p(rec), ctypes.byref(nf), _p(lv)))
+        return rec, lv
+
     def dump_sorted(self):
         m = np.zeros(self.num_prims, np.uint32)
         o = np.zeros(self.num_prims, np.uint32)
@@ -311,6 +321,13 @@ class _Integrator:
     def solution(self):
         f = self.film(CH_SOLUTION)
         return f[..., :3] / np.maximum(f[..., 4:5], 1e-30)
+
+    @property
+    def l2_window_bytes(self):
+        """bytes of top-level LBVH records pinned in L2 for this integrator's stream (0: the tree fits the L2)"""
+        n = c_u64()
+        check(_lib.load().wost_l2_window_bytes(self.h, ctypes.byref(n)))
+        return n.value
 
     @property
     def launch_count(self):

@@ -805,21 +805,24 @@ namespace wost
         }
         const int r = threadIdx.x;
         {
-            const uint4 *src = reinterpret_cast<const uint4 *>(net.mlp);
-            uint4 *dst = reinterpret_cast<uint4 *>(sm.w);
-            for (int i = r; i < MlpTrainSmem<K0>::kWeightHalfs / 8; i += blockDim.x)
-                dst[i] = __ldg(src + i);
+            uint64_t *wbar = sm.bar + 2;
             if (r == 0)
             {
                 tc::mbar_init(sm.bar, 1);
+                tc::mbar_init(wbar, 1);
                 tc::fence_mbar_init();
+                // forward weights: one TMA bulk copy (mlp_tc.cuh: bulk_g2s)
+                constexpr uint32_t kWBytes = (uint32_t)MlpTrainSmem<K0>::kWeightHalfs * 2u;
+                static_assert(kWBytes % 16u == 0u, "bulk copy size");
+                tc::mbar_expect_tx(wbar, kWBytes);
+                tc::bulk_g2s(sm.w, net.mlp, kWBytes, wbar);
             }
             if (r < 32)
                 tc::tmem_alloc(sm.tmem_slot, 512);
-            tc::fence_proxy_async();
             tc::tc_fence_before();
             __syncthreads();
             tc::tc_fence_after();
+            tc::mbar_wait(wbar, 0);
         }
         const uint32_t tmem = *sm.tmem_slot;
         const uint32_t lane_base = tmem + ((uint32_t)(r & ~31) << 16);

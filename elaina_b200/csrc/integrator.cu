@@ -535,6 +535,43 @@ namespace wost
         }
         return WOST_OK;
     }
+    // Blackwell L2 persistence for the top BVH levels: when the Dirichlet tree (fused records + leaf records) does not fit
+    // the L2, the contiguous slab of its top levels (scene.cu: breadth-first record order, <= 32 MB) gets a persisting
+    // access-policy window on the integrator's stream; everything else on the stream is demoted to streaming, so the records
+    // every descent reads stay resident while leaf records and accumulators flow through. WOST_L2_PERSIST=0 disables it.
+    static void apply_l2_window(wost_integrator *it)
+    {
+        it->l2_window_bytes = 0;
+        const wost_scene *sc = it->problem->dirichlet;
+        const char *e = getenv("WOST_L2_PERSIST");
+        if (!sc || sc->nprims < 2 || (e && atoi(e) == 0))
+            return;
+        int l2 = 0, max_persist = 0, max_window = 0;
+        cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, it->device);
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, it->device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, it->device);
+        const size_t leaf_bytes = (size_t)sc->nprims * (sc->dim == 2 ? sizeof(LeafPrim<2>) : sizeof(LeafPrim<3>));
+        const bool force = e && atoi(e) >= 2; // 2: also for trees that fit (A/B measurements)
+        if ((!force && sc->tnode_bytes() + leaf_bytes <= (size_t)l2) || max_persist <= 0 || max_window <= 0)
+            return;
+        const size_t bytes = std::min(std::min(sc->top_bytes(), (size_t)max_window), (size_t)max_persist);
+        if (bytes == 0 || cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes) != cudaSuccess)
+        {
+            cudaGetLastError();
+            return;
+        }
+        cudaStreamAttrValue v;
+        memset(&v, 0, sizeof(v));
+        v.accessPolicyWindow.base_ptr = sc->d_tnodes.ptr;
+        v.accessPolicyWindow.num_bytes = bytes;
+        v.accessPolicyWindow.hitRatio = 1.0f;
+        v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        if (cudaStreamSetAttribute(it->stream, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess)
+            it->l2_window_bytes = bytes;
+        else
+            cudaGetLastError();
+    }
     template <int D, bool RefOrder, int F>
     static wost_status solve_persistent_f(wost_integrator *it, uint64_t *walk_steps);
     // picks the kernel variant compiled for the features this problem has (walk.cuh: kFeatNeumann / kFeatSource); the
@@ -854,6 +891,7 @@ extern "C"
         if (cudaStreamCreateWithFlags(&it->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&it->ev0) != cudaSuccess ||
             cudaEventCreate(&it->ev1) != cudaSuccess)
             return fail("stream/event creation");
+        apply_l2_window(it);
         if (cudaDeviceSynchronize() != cudaSuccess)
             return fail("sync");
         *out = it;
@@ -1006,6 +1044,13 @@ extern "C"
         WOST_CUDA_TRY(cudaMemcpy(out16, it->d_overflow.ptr + 8, 16 * sizeof(int), cudaMemcpyDeviceToHost));
         WOST_CUDA_TRY(cudaMemcpy(out16 + 16, it->d_overflow.ptr + 32, 32 * sizeof(int), cudaMemcpyDeviceToHost));
         WOST_CUDA_TRY(cudaMemset(it->d_overflow.ptr + 8, 0, 88 * sizeof(int)));
+        return WOST_OK;
+    }
+    wost_status wost_l2_window_bytes(wost_integrator *it, uint64_t *bytes)
+    {
+        if (!it || !bytes)
+            return WOST_ERR_INVALID;
+        *bytes = (uint64_t)it->l2_window_bytes;
         return WOST_OK;
     }
     wost_status wost_last_launch_count(wost_integrator *it, uint64_t *kernel_launches)

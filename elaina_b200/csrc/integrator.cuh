@@ -66,6 +66,7 @@ struct wost_integrator
     float last_loss = 0.0f;
     std::vector<cudaEvent_t> prof_ev; // WOST_PROFILE=1
     float prof_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    size_t l2_window_bytes = 0; // top-level LBVH records pinned in L2 through the stream's access-policy window (0: tree fits L2)
 
     // progressive metrics: is sample index `sid` one the reference dumps (uniform/integrator.cu:577-609)? bit 0 spp, bit 1 time
     int frame_kinds(int sid) const
@@ -102,6 +103,8 @@ struct wost_integrator
             cudaEventDestroy(ev1);
         if (stream)
             cudaStreamDestroy(stream);
+        if (l2_window_bytes)
+            cudaCtxResetPersistingL2Cache();
     }
 };
 

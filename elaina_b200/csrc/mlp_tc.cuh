@@ -46,6 +46,19 @@ namespace wost
                     : "memory");
             } while (!done);
         }
+        // TMA bulk copy (1-D, cp.async.bulk): one thread moves `bytes` (multiple of 16, both addresses 16-byte aligned) from
+        // global to shared memory through the async proxy and the mbarrier counts the bytes -- the same proxy tcgen05.mma reads
+        // operands through, so no generic-proxy staging loop and no proxy fence for the weights
+        WOST_DEV void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+        {
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+        }
+        WOST_DEV void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar)
+        {
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                         "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                         : "memory");
+        }
         WOST_DEV void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
         WOST_DEV void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
         WOST_DEV void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -153,21 +166,24 @@ namespace wost
     template <int K0>
     WOST_DEV uint32_t mlp_fwd_setup(MlpFwdSmem<K0> &sm, const __half *weights_canonical)
     {
-        const uint4 *src = reinterpret_cast<const uint4 *>(weights_canonical);
-        uint4 *dst = reinterpret_cast<uint4 *>(sm.w);
-        for (int i = threadIdx.x; i < MlpFwdSmem<K0>::kWeightHalfs / 8; i += blockDim.x)
-            dst[i] = __ldg(src + i);
+        uint64_t *wbar = sm.bar + 2; // second mbarrier of the sync words: weight arrival
         if (threadIdx.x == 0)
         {
             tc::mbar_init(sm.bar, 1);
+            tc::mbar_init(wbar, 1);
             tc::fence_mbar_init();
+            // weights: ONE TMA bulk copy (26 KB, already in the canonical UMMA layout in global memory)
+            constexpr uint32_t kWBytes = (uint32_t)MlpFwdSmem<K0>::kWeightHalfs * 2u;
+            static_assert(kWBytes % 16u == 0u, "bulk copy size");
+            tc::mbar_expect_tx(wbar, kWBytes);
+            tc::bulk_g2s(sm.w, weights_canonical, kWBytes, wbar);
         }
         if (threadIdx.x < 32)
             tc::tmem_alloc(sm.tmem_slot, kTmemColsFwd);
-        tc::fence_proxy_async(); // weights were written through the generic proxy, tcgen05.mma reads through the async proxy
         tc::tc_fence_before();
         __syncthreads();
         tc::tc_fence_after();
+        tc::mbar_wait(wbar, 0);
         return *sm.tmem_slot;
     }
     template <int K0>

@@ -15,6 +15,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
+#include <cstring>
 #include <algorithm>
 #include <mutex>
 #include <unordered_map>
@@ -471,7 +472,7 @@ namespace wost
     WOST_DEV int cub_bits(unsigned long long a, unsigned long long b) { return __clzll(a ^ b); }
     // core/bvh.cuh:110-229 (Karras 2012)
     template <typename U>
-    __global__ void k_karras(int n, const U *code, Node *nodes, int *leaf_count)
+    __global__ void k_karras(int n, const U *code, Node *nodes, int *leaf_count, int *leaf_first)
     {
         const int idx = blockIdx.x * blockDim.x + threadIdx.x;
         if (idx >= n - 1)
@@ -548,6 +549,7 @@ namespace wost
         if (last == gamma + 1)
             R += n - 1;
         leaf_count[idx] = last - first + 1;
+        leaf_first[idx] = first;
         nodes[idx].left = L;
         nodes[idx].right = R;
         nodes[idx].object = kInvalid;
@@ -656,13 +658,254 @@ namespace wost
         rank[i] = r;
     }
 
+
+    // ------------------------------------------------------------------ oriented boxes of the traversal records (lbvh.cuh: Obb)
+    constexpr int kObbFloats2 = 6, kObbFloats3 = 12;
+    template <int D>
+    constexpr int obb_floats() { return D == 2 ? kObbFloats2 : kObbFloats3; }
+    WOST_DEV Vec<2> prim_weighted_normal(const LeafPrim<2> &p)
+    {
+        Vec<2> n;
+        n[0] = p.p[1] - p.p[3], n[1] = p.p[2] - p.p[0]; // perpendicular of pb - pa, length = segment length
+        return n;
+    }
+    WOST_DEV Vec<3> prim_weighted_normal(const LeafPrim<3> &p)
+    {
+        Vec<3> a, b;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            a[k] = p.p[3 + k] - p.p[k], b[k] = p.p[6 + k] - p.p[k];
+        return vcross(a, b); // length = 2 x area
+    }
+    // (1) frame: length / area weighted normals summed bottom-up (the second thread to reach a node merges its children,
+    // like the refits). The right child's sum is flipped when it opposes the left one: stroke soups are not consistently
+    // oriented, and the sign of a slab normal does not matter.
+    template <int D>
+    __global__ void k_obb_normals(int n, const Node *nodes, const LeafPrim<D> *lp, float *nsum, int *flags)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n)
+            return;
+        const Vec<D> w = prim_weighted_normal(lp[i]);
+        const size_t leaf = (size_t)(n - 1) + i;
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            nsum[leaf * D + k] = w[k];
+        uint32_t parent = nodes[leaf].parent;
+        while (parent != kInvalid)
+        {
+            __threadfence();
+            const int old = atomicAdd(flags + parent, 1);
+            if (old == 0)
+                return;
+            const size_t l = nodes[parent].left, r = nodes[parent].right;
+            float a[D], b[D], dot = 0.0f;
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+            {
+                a[k] = __ldcg(nsum + l * D + k);
+                b[k] = __ldcg(nsum + r * D + k);
+                dot = dot + a[k] * b[k];
+            }
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+                nsum[(size_t)parent * D + k] = (dot >= 0.0f) ? a[k] + b[k] : a[k] - b[k];
+            parent = nodes[parent].parent;
+        }
+    }
+    WOST_DEV Obb<2> obb_frame(const float *ns, const LeafPrim<2> *)
+    {
+        Obb<2> o;
+        const float len = dm_sqrt(ns[0] * ns[0] + ns[1] * ns[1]);
+        if (len > 0.0f && len < dm_inf())
+            o.ax[0] = dm_div(ns[0], len), o.ax[1] = dm_div(ns[1], len);
+        else
+            o.ax[0] = 1.0f, o.ax[1] = 0.0f;
+        return o;
+    }
+    // 3D: n = normalised sum; in-plane axis t = the longest edge (single triangle) or the coordinate axis least aligned with n,
+    // made orthogonal to n (Gram-Schmidt)
+    WOST_DEV Obb<3> obb_frame(const float *ns, const LeafPrim<3> *single)
+    {
+        Obb<3> o;
+        const float len = dm_sqrt(ns[0] * ns[0] + ns[1] * ns[1] + ns[2] * ns[2]);
+        if (len > 0.0f && len < dm_inf())
+            o.n[0] = dm_div(ns[0], len), o.n[1] = dm_div(ns[1], len), o.n[2] = dm_div(ns[2], len);
+        else
+            o.n[0] = 0.0f, o.n[1] = 0.0f, o.n[2] = 1.0f;
+        float e[3] = {0.0f, 0.0f, 0.0f};
+        bool have = false;
+        if (single)
+        {
+            float bestl = 0.0f;
+            for (int a = 0; a < 3; ++a)
+            {
+                const int b = (a + 1) % 3;
+                const float dx = single->p[3 * b] - single->p[3 * a], dy = single->p[3 * b + 1] - single->p[3 * a + 1], dz = single->p[3 * b + 2] - single->p[3 * a + 2];
+                const float l2 = dx * dx + dy * dy + dz * dz;
+                if (l2 > bestl && l2 < dm_inf())
+                    bestl = l2, e[0] = dx, e[1] = dy, e[2] = dz, have = true;
+            }
+        }
+        for (int attempt = 0; attempt < 2; ++attempt)
+        {
+            if (!have)
+            {
+                const float ax = dm_abs(o.n[0]), ay = dm_abs(o.n[1]), az = dm_abs(o.n[2]);
+                const int k = (ax <= ay && ax <= az) ? 0 : (ay <= az ? 1 : 2);
+                e[0] = e[1] = e[2] = 0.0f;
+                e[k] = 1.0f;
+            }
+            const float dn = e[0] * o.n[0] + e[1] * o.n[1] + e[2] * o.n[2];
+            const float tx = e[0] - dn * o.n[0], ty = e[1] - dn * o.n[1], tz = e[2] - dn * o.n[2];
+            const float tl = dm_sqrt(tx * tx + ty * ty + tz * tz);
+            if (tl > 1e-20f && tl < dm_inf() && (have ? tl * tl > 0.25f * (e[0] * e[0] + e[1] * e[1] + e[2] * e[2]) : true))
+            {
+                o.t[0] = dm_div(tx, tl), o.t[1] = dm_div(ty, tl), o.t[2] = dm_div(tz, tl);
+                return o;
+            }
+            have = false; // degenerate triangle: fall back to the coordinate axis
+        }
+        o.t[0] = 1.0f, o.t[1] = 0.0f, o.t[2] = 0.0f; // unreachable for a unit n
+        return o;
+    }
+    // (2) extents: G threads (1, a warp, a CTA) per node project every vertex of the node's leaf range onto the frame
+    // (coalesced reads of the Morton-ordered leaf records) and keep the exact fp32 min / max, widened by 2^-20 max|coordinate|.
+    // Nodes are dealt to the three variants by the size of their range (lo_count < count <= hi_count).
+    template <int D, int G>
+    __global__ void __launch_bounds__(256) k_obb_extents(int n, const int *leaf_first, const int *leaf_count, const LeafPrim<D> *lp, const float *nsum,
+                                                                      const float *ext, float *obb, int lo_count, int hi_count)
+    {
+        constexpr int F = D == 2 ? kObbFloats2 : kObbFloats3;
+        const int NN = 2 * n - 1;
+        long long node;
+        int lane;
+        if (G == 1)
+            node = (long long)blockIdx.x * blockDim.x + threadIdx.x, lane = 0;
+        else if (G == 32)
+            node = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+        else
+            node = blockIdx.x, lane = threadIdx.x;
+        if (node >= (G == 1 ? NN : n - 1))
+            return;
+        const bool is_leaf = node >= n - 1;
+        const int first = is_leaf ? (int)(node - (n - 1)) : leaf_first[node];
+        const int count = is_leaf ? 1 : leaf_count[node];
+        if (count <= lo_count || count > hi_count)
+            return;
+        float ns[D];
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            ns[k] = nsum[(size_t)node * D + k];
+        Obb<D> o = obb_frame(ns, is_leaf ? lp + first : (const LeafPrim<D> *)nullptr);
+        float mn[D], mx[D];
+#pragma unroll
+        for (int k = 0; k < D; ++k)
+            mn[k] = dm_inf(), mx[k] = -dm_inf();
+        for (int j = lane; j < count; j += G)
+        {
+            const LeafPrim<D> p = lp[(size_t)first + j];
+#pragma unroll
+            for (int v = 0; v < D; ++v)
+            {
+                Vec<D> x;
+#pragma unroll
+                for (int k = 0; k < D; ++k)
+                    x[k] = p.p[v * D + k];
+                float pr[D];
+                obb_project(o, x, pr);
+#pragma unroll
+                for (int k = 0; k < D; ++k)
+                    mn[k] = fmin_nn(mn[k], pr[k]), mx[k] = fmax_nn(mx[k], pr[k]);
+            }
+        }
+        if constexpr (G > 1)
+        {
+#pragma unroll
+            for (int k = 0; k < D; ++k)
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1)
+                {
+                    mn[k] = fmin_nn(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], off));
+                    mx[k] = fmax_nn(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], off));
+                }
+        }
+        if constexpr (G > 32)
+        {
+            __shared__ float sm[2 * D][G / 32];
+            if ((threadIdx.x & 31) == 0)
+#pragma unroll
+                for (int k = 0; k < D; ++k)
+                    sm[k][threadIdx.x >> 5] = mn[k], sm[D + k][threadIdx.x >> 5] = mx[k];
+            __syncthreads();
+            if (threadIdx.x == 0)
+                for (int w = 1; w < G / 32; ++w)
+#pragma unroll
+                    for (int k = 0; k < D; ++k)
+                        mn[k] = fmin_nn(mn[k], sm[k][w]), mx[k] = fmax_nn(mx[k], sm[D + k][w]);
+        }
+        if (lane != 0)
+            return;
+        float m = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 2 * D; ++k)
+            m = fmax_nn(m, dm_abs(ext[k])); // node 0 = exact extents of the whole mesh
+        const float wdn = m * 9.5367431640625e-07f; // 2^-20
+        float *dst = obb + (size_t)node * F;
+        if constexpr (D == 2)
+        {
+            const Obb<2> &q = o;
+            dst[0] = q.ax[0], dst[1] = q.ax[1];
+            dst[2] = mn[0] - wdn, dst[3] = mx[0] + wdn, dst[4] = mn[1] - wdn, dst[5] = mx[1] + wdn;
+        }
+        else
+        {
+            const Obb<3> &q = o;
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                dst[k] = q.n[k], dst[3 + k] = q.t[k], dst[6 + k] = mn[k] - wdn, dst[9 + k] = mx[k] + wdn;
+        }
+    }
+
+    // ------------------------------------------------------------------ record order: top levels first
+    // The fused records are stored in breadth-first order for the top levels of the tree (depth < top_depth) and in Karras
+    // order below: the records every query reads -- the first ~17 of the ~20 levels of a descent -- form one contiguous slab
+    // at the start of the array, which the integrators pin in L2 with an access-policy window when the whole tree does not
+    // fit (integrator.cu: apply_l2_window; c4: 280 MB of records against 126 MB of L2). Canonical arrays keep Karras order.
+    __global__ void k_node_depth(int n, const Node *nodes, int *depth, int *hist)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n - 1)
+            return;
+        int d = 0;
+        for (uint32_t p = nodes[i].parent; p != kInvalid; p = nodes[p].parent)
+            ++d;
+        depth[i] = d;
+        atomicAdd(hist + min(d, 63), 1);
+    }
+    __global__ void k_bfs_keys(int n, const int *depth, int top_depth, unsigned long long *key, uint32_t *val)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n - 1)
+            return;
+        key[i] = ((unsigned long long)min(depth[i], top_depth) << 32) | (unsigned long long)(uint32_t)i;
+        val[i] = (uint32_t)i;
+    }
+    __global__ void k_perm_scatter(int n, const uint32_t *sorted_old, uint32_t *perm)
+    {
+        const int j = blockIdx.x * blockDim.x + threadIdx.x;
+        if (j >= n - 1)
+            return;
+        perm[sorted_old[j]] = (uint32_t)j;
+    }
+
     // ------------------------------------------------------------------ traversal layout
     WOST_DEV uint32_t child_ref(const Node *nodes, uint32_t child, int n)
     {
         return (nodes[child].object != kInvalid) ? ((child - (uint32_t)(n - 1)) | kLeafFlag) : child;
     }
     template <int D>
-    __global__ void k_layout_internal(int n, const Node *nodes, const float *ext, const float *cones, TNode<D> *tn, CNode<D> *cn)
+    __global__ void k_layout_internal(int n, const Node *nodes, const float *ext, const float *cones, const float *obb, const uint32_t *perm, TNode<D> *tn, CNode<D> *cn)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x;
         if (i >= n - 1)
@@ -677,9 +920,27 @@ namespace wost
         }
         t.lref = child_ref(nodes, l, n);
         t.rref = child_ref(nodes, r, n);
-        t.pad0 = 0;
-        t.pad1 = 0;
-        tn[i] = t;
+        if (!(t.lref & kLeafFlag))
+            t.lref = perm[t.lref];
+        if (!(t.rref & kLeafFlag))
+            t.rref = perm[t.rref];
+        const uint32_t dst = perm[i];
+        {
+            constexpr int F = D == 2 ? kObbFloats2 : kObbFloats3;
+            float *raw = reinterpret_cast<float *>(&t);
+            constexpr int l0 = D == 2 ? 10 : 16; // float offset of the left child's oriented box inside the record
+#pragma unroll
+            for (int k = 0; k < F; ++k)
+            {
+                raw[l0 + k] = obb[(size_t)l * F + k];
+                raw[l0 + F + k] = obb[(size_t)r * F + k];
+            }
+            if (D == 2)
+                raw[22] = raw[23] = 0.0f;
+            else
+                raw[14] = raw[15] = 0.0f;
+        }
+        tn[dst] = t;
         CNode<D> c;
 #pragma unroll
         for (int k = 0; k < D + 2; ++k)
@@ -693,7 +954,7 @@ namespace wost
             pad[0] = 0.0f;
             pad[1] = 0.0f;
         }
-        cn[i] = c;
+        cn[dst] = c;
     }
     WOST_DEV void fill_sil(LeafSil<2> &o, const float *verts, const int *rec)
     {
@@ -981,7 +1242,8 @@ namespace wost
         cudaStream_t st = 0;
         DevBuf<float> lboxes, lcones, partial;
         DevBuf<uint32_t> code_in, idx_in;
-        DevBuf<int> flags, dup, leaf_count;
+        DevBuf<int> flags, dup, leaf_count, leaf_first;
+        DevBuf<float> nsum, obb;
         DevBuf<float> ext;
         DevBuf<unsigned long long> key64;
         DevBuf<char> temp;
@@ -996,6 +1258,7 @@ namespace wost
         WOST_CUDA_TRY(s->d_cones.alloc((size_t)NN * (D + 2)));
         WOST_CUDA_TRY(flags.alloc(std::max(1, n - 1)));
         WOST_CUDA_TRY(leaf_count.alloc(std::max(1, n - 1)));
+        WOST_CUDA_TRY(leaf_first.alloc(std::max(1, n - 1)));
         WOST_CUDA_TRY(ext.alloc((size_t)NN * 2 * D));
         WOST_CUDA_TRY(s->d_leaf_rank.alloc(n));
         WOST_CUDA_TRY(dup.alloc(1));
@@ -1027,10 +1290,10 @@ namespace wost
             {
                 WOST_CUDA_TRY(key64.alloc(n));
                 k_keys64<<<div_up(n, B), B, 0, st>>>(n, s->d_morton.ptr, s->d_order.ptr, key64.ptr);
-                k_karras<unsigned long long><<<div_up(n - 1, B), B, 0, st>>>(n, key64.ptr, s->d_nodes.ptr, leaf_count.ptr);
+                k_karras<unsigned long long><<<div_up(n - 1, B), B, 0, st>>>(n, key64.ptr, s->d_nodes.ptr, leaf_count.ptr, leaf_first.ptr);
             }
             else
-                k_karras<uint32_t><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_morton.ptr, s->d_nodes.ptr, leaf_count.ptr);
+                k_karras<uint32_t><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_morton.ptr, s->d_nodes.ptr, leaf_count.ptr, leaf_first.ptr);
             WOST_CUDA_TRY(cudaMemsetAsync(flags.ptr, 0, sizeof(int) * (size_t)(n - 1), st));
             k_refit_boxes<D><<<div_up(n, B), B, 0, st>>>(n, s->d_nodes.ptr, s->d_boxes.ptr, flags.ptr);
             WOST_CUDA_TRY(cudaMemsetAsync(flags.ptr, 0, sizeof(int) * (size_t)(n - 1), st));
@@ -1049,12 +1312,53 @@ namespace wost
         WOST_CUDA_TRY(s->d_leaf_prim.alloc(sizeof(LeafPrim<D>) * (size_t)n));
         WOST_CUDA_TRY(s->d_leaf_sil.alloc(sizeof(LeafSil<D>) * (size_t)n * D));
         WOST_CUDA_TRY(s->d_leaf_obj.alloc(n));
-        if (n > 1)
-            k_layout_internal<D><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_nodes.ptr, ext.ptr, s->d_cones.ptr,
-                                                                  reinterpret_cast<TNode<D> *>(s->d_tnodes.ptr), reinterpret_cast<CNode<D> *>(s->d_cnodes.ptr));
         k_layout_leaves<D><<<div_up(n, B), B, 0, st>>>(n, s->d_order.ptr, s->d_verts.ptr, s->d_prims.ptr, s->d_sil_rec.ptr, s->d_prim_sil.ptr,
                                                        reinterpret_cast<LeafPrim<D> *>(s->d_leaf_prim.ptr), s->d_leaf_obj.ptr,
                                                        reinterpret_cast<LeafSil<D> *>(s->d_leaf_sil.ptr));
+        if (n > 1)
+        {
+            // oriented boxes of every node (pruning bound of the closest-point query, lbvh.cuh: Obb)
+            const LeafPrim<D> *lp = reinterpret_cast<const LeafPrim<D> *>(s->d_leaf_prim.ptr);
+            WOST_CUDA_TRY(nsum.alloc((size_t)NN * D));
+            WOST_CUDA_TRY(obb.alloc((size_t)NN * obb_floats<D>()));
+            WOST_CUDA_TRY(cudaMemsetAsync(flags.ptr, 0, sizeof(int) * (size_t)(n - 1), st));
+            k_obb_normals<D><<<div_up(n, B), B, 0, st>>>(n, s->d_nodes.ptr, lp, nsum.ptr, flags.ptr);
+            constexpr int kSmall = 8, kMedium = 1024;
+            k_obb_extents<D, 1><<<div_up(NN, 256), 256, 0, st>>>(n, leaf_first.ptr, leaf_count.ptr, lp, nsum.ptr, ext.ptr, obb.ptr, 0, kSmall);
+            k_obb_extents<D, 32><<<div_up(n - 1, 256 / 32), 256, 0, st>>>(n, leaf_first.ptr, leaf_count.ptr, lp, nsum.ptr, ext.ptr, obb.ptr, kSmall, kMedium);
+            k_obb_extents<D, 256><<<n - 1, 256, 0, st>>>(n, leaf_first.ptr, leaf_count.ptr, lp, nsum.ptr, ext.ptr, obb.ptr, kMedium, 0x7fffffff);
+            // record order: breadth-first for the top levels (as many levels as fit the L2 window budget), Karras order below
+            DevBuf<int> depth, hist;
+            DevBuf<unsigned long long> bkey_in, bkey_out;
+            DevBuf<uint32_t> bval_in, bval_out, perm;
+            WOST_CUDA_TRY(depth.alloc(n - 1));
+            WOST_CUDA_TRY(hist.alloc(64));
+            WOST_CUDA_TRY(bkey_in.alloc(n - 1));
+            WOST_CUDA_TRY(bkey_out.alloc(n - 1));
+            WOST_CUDA_TRY(bval_in.alloc(n - 1));
+            WOST_CUDA_TRY(bval_out.alloc(n - 1));
+            WOST_CUDA_TRY(perm.alloc(n - 1));
+            WOST_CUDA_TRY(cudaMemsetAsync(hist.ptr, 0, 64 * sizeof(int), st));
+            k_node_depth<<<div_up(n - 1, B), B, 0, st>>>(n, s->d_nodes.ptr, depth.ptr, hist.ptr);
+            int h_hist[64];
+            WOST_CUDA_TRY(cudaMemcpyAsync(h_hist, hist.ptr, sizeof(h_hist), cudaMemcpyDeviceToHost, st));
+            WOST_CUDA_TRY(cudaStreamSynchronize(st));
+            int top_depth = 0;
+            size_t top_nodes = 0;
+            while (top_depth < 63 && (top_nodes + (size_t)h_hist[top_depth]) * sizeof(TNode<D>) <= kL2WindowBudget)
+                top_nodes += (size_t)h_hist[top_depth++];
+            s->top_nodes = (int)top_nodes;
+            s->top_depth = top_depth;
+            k_bfs_keys<<<div_up(n - 1, B), B, 0, st>>>(n, depth.ptr, top_depth, bkey_in.ptr, bval_in.ptr);
+            size_t tb2 = 0;
+            WOST_CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tb2, bkey_in.ptr, bkey_out.ptr, bval_in.ptr, bval_out.ptr, n - 1, 0, 40, st));
+            DevBuf<char> temp2;
+            WOST_CUDA_TRY(temp2.alloc(tb2));
+            WOST_CUDA_TRY(cub::DeviceRadixSort::SortPairs(temp2.ptr, tb2, bkey_in.ptr, bkey_out.ptr, bval_in.ptr, bval_out.ptr, n - 1, 0, 40, st));
+            k_perm_scatter<<<div_up(n - 1, B), B, 0, st>>>(n, bval_out.ptr, perm.ptr);
+            k_layout_internal<D><<<div_up(n - 1, B), B, 0, st>>>(n, s->d_nodes.ptr, ext.ptr, s->d_cones.ptr, obb.ptr, perm.ptr,
+                                                                  reinterpret_cast<TNode<D> *>(s->d_tnodes.ptr), reinterpret_cast<CNode<D> *>(s->d_cnodes.ptr));
+        }
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_box, s->d_boxes.ptr, sizeof(float) * 2 * D, cudaMemcpyDeviceToHost, st));
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_cone, s->d_cones.ptr, sizeof(float) * (D + 2), cudaMemcpyDeviceToHost, st));
         WOST_CUDA_TRY(cudaMemcpyAsync(s->root_ext, ext.ptr, sizeof(float) * 2 * D, cudaMemcpyDeviceToHost, st));
@@ -1303,6 +1607,26 @@ extern "C"
             WOST_CUDA_TRY(cudaMemcpy(aabbs, s->d_boxes.ptr, NN * 2 * s->dim * sizeof(float), cudaMemcpyDeviceToHost));
         if (cones)
             WOST_CUDA_TRY(cudaMemcpy(cones, s->d_cones.ptr, NN * (s->dim + 2) * sizeof(float), cudaMemcpyDeviceToHost));
+        return WOST_OK;
+    }
+    wost_status wost_scene_dump_traversal_layout(const wost_scene *s, float *records, int *record_floats, float *leaf_verts)
+    {
+        if (!s)
+            return WOST_ERR_INVALID;
+        const size_t rec = s->dim == 2 ? sizeof(TNode<2>) : sizeof(TNode<3>);
+        const size_t leaf = s->dim == 2 ? sizeof(LeafPrim<2>) : sizeof(LeafPrim<3>);
+        if (record_floats)
+            *record_floats = (int)(rec / sizeof(float));
+        if (records && s->nprims > 1)
+            WOST_CUDA_TRY(cudaMemcpy(records, s->d_tnodes.ptr, rec * (size_t)(s->nprims - 1), cudaMemcpyDeviceToHost));
+        if (leaf_verts && s->nprims > 0)
+        {
+            std::vector<char> raw(leaf * (size_t)s->nprims);
+            WOST_CUDA_TRY(cudaMemcpy(raw.data(), s->d_leaf_prim.ptr, raw.size(), cudaMemcpyDeviceToHost));
+            const int nf = s->dim * s->dim;
+            for (int i = 0; i < s->nprims; ++i)
+                memcpy(leaf_verts + (size_t)i * nf, raw.data() + (size_t)i * leaf, sizeof(float) * nf);
+        }
         return WOST_OK;
     }
     wost_status wost_scene_traversal_stats(const wost_scene *s, uint64_t *full_reference_order, uint64_t *restricted_second_pass, int reset)

@@ -28,6 +28,9 @@ struct wost_scene
     float root_box[6] = {0, 0, 0, 0, 0, 0};
     float root_cone[5] = {0, 0, 0, 0, 0};
     float root_ext[6] = {0, 0, 0, 0, 0, 0}; // exact (unpadded) extents of the whole mesh
+    int top_nodes = 0, top_depth = 0;       // the first top_nodes fused records are the levels [0, top_depth) in breadth-first order
+    size_t tnode_bytes() const { return (size_t)std::max(0, nprims - 1) * (dim == 2 ? sizeof(wost::TNode<2>) : sizeof(wost::TNode<3>)); }
+    size_t top_bytes() const { return (size_t)top_nodes * (dim == 2 ? sizeof(wost::TNode<2>) : sizeof(wost::TNode<3>)); }
 
     template <int D>
     wost::DevBVH<D> view() const
@@ -54,6 +57,7 @@ struct wost_scene
 
 namespace wost
 {
+    constexpr size_t kL2WindowBudget = 32u << 20; // bytes of top-level records kept contiguous (and pinned in L2 for trees beyond L2)
     template <int D>
     inline DevBVH<D> empty_bvh()
     {

@@ -48,6 +48,10 @@ extern "C"
      * nodes num_nodes*4 u32 (parent,left,right,object), aabbs num_nodes*2*dim (upper,lower), cones num_nodes*(dim+2) */
     wost_status wost_scene_dump_bvh(const wost_scene *scene, uint32_t *nodes, float *aabbs, float *cones);
     wost_status wost_scene_dump_sorted(const wost_scene *scene, uint32_t *morton, uint32_t *object_idx);
+    /* diagnostics of the B200 traversal layout (no reference counterpart): the fused internal-node records
+     * (num_prims-1 records of *record_floats floats: both children's exact extents, child references and oriented boxes,
+     * csrc/lbvh.cuh TNode) and the Morton-ordered leaf vertices (num_prims * dim * dim floats). Either pointer may be NULL. */
+    wost_status wost_scene_dump_traversal_layout(const wost_scene *scene, float *records, int *record_floats, float *leaf_verts);
     /* Closest-point traversal statistics of the parity probes on this scene since the last reset: queries that ran a FULL
      * traversal in the reference's visit order (3D far field only) and queries that finished with the restricted
      * reference-order second pass (near-ties in 3D, and in 2D beyond |q| ~ 2000 where the reference's 1e-3 box padding no
@@ -184,6 +188,9 @@ extern "C"
     /* diagnostics, meaningful only when the library was built with -DWOST_TRAV_DEBUG: closest-point trips [0..7] and queries
      * [8..15] of this integrator per decade of the query's max |coordinate| (<600, <2e3, <1e4, ..., >=1e8); read and reset */
     wost_status wost_debug_counters(wost_integrator *it, unsigned int *out16);
+    /* bytes of top-level LBVH records this integrator pinned in L2 (cudaAccessPolicyWindow on its stream; 0 when the tree
+     * fits the L2 or WOST_L2_PERSIST=0) -- north_star (2), no reference counterpart (the reference leaves L2 to the hardware) */
+    wost_status wost_l2_window_bytes(wost_integrator *it, uint64_t *bytes);
     /* counters of the last solve */
     wost_status wost_last_launch_count(wost_integrator *it, uint64_t *kernel_launches);
     /* launches of the fused walk-step kernel in the last solve and their summed device time (CUDA events on the
@@ -225,6 +232,31 @@ extern "C"
      * callback must enqueue a SUM all-reduce on `stream` (a cudaStream_t) and return 0. */
     typedef int (*wost_allreduce_fn)(void *user, void *d_buf, uint64_t n_floats, void *stream);
     wost_status wost_set_allreduce(wost_integrator *it, wost_allreduce_fn fn, void *user);
+
+    /* ------------------------------------------------------------------ multi-GPU: NCCL inside the library
+     * The reference is single-device (core/device/context.cpp:23-24 hard-codes device 0), so these entry points have no
+     * counterpart to mirror; they are what a multi-GPU exec.cu needs (north_star: evaluation points shard across the GPUs
+     * of one box, NCCL only for the gradient all-reduce of the replicated guiding network and the final grid gather).
+     * One process per GPU. libnccl.so.2 is resolved at run time (dlopen; WOST_NCCL_LIB overrides the search). */
+    typedef struct wost_comm wost_comm;
+    /* rank 0: 128-byte NCCL unique id, to be handed to the other ranks by the launcher (torch.distributed broadcast, MPI, file) */
+    wost_status wost_comm_unique_id(void *id128);
+    /* collective over `world` processes; uses the calling thread's current CUDA device */
+    wost_status wost_comm_create(int rank, int world, const void *id128, wost_comm **out);
+    /* torchrun / mpirun environment (RANK, WORLD_SIZE, LOCAL_RANK, MASTER_PORT | OMPI_COMM_WORLD_*): selects device LOCAL_RANK and
+     * exchanges the id through a file in $TMPDIR named after the launcher. *out = NULL (and WOST_OK) for a single process. */
+    wost_status wost_comm_create_from_env(wost_comm **out);
+    void wost_comm_destroy(wost_comm *comm);
+    wost_status wost_comm_info(const wost_comm *comm, int *rank, int *world, int *nccl_version);
+    /* fills pixel_stride_rows / num_shards / shard of `settings` for this rank (interleaved tiles of stride_rows rows) */
+    wost_status wost_comm_shard_settings(const wost_comm *comm, wost_settings *settings, int stride_rows);
+    /* guided integrator: ncclAllReduce(sum) of the gradient slab on the integrator's stream before every optimiser step */
+    wost_status wost_integrator_set_comm(wost_integrator *it, wost_comm *comm);
+    /* final grid gather: the row tiles every rank evaluated are collected into the device film of rank `root` (root < 0: of
+     * every rank) -- (N-1)/N of one film over NVLink, packed rows, grouped send/recv or one all-gather */
+    wost_status wost_film_gather(wost_integrator *it, wost_comm *comm, int channel, int root);
+    /* host scalars across ranks: sum (op_max = 0) or max (op_max = 1) */
+    wost_status wost_comm_allreduce_f64(wost_comm *comm, double *vals, int n, int op_max);
 
     /* NanoVDB source grids (core/problem.cu:135-149 reads them with nanovdb::io::readGrid; the walker samples them with
      * worldToIndex + SampleFromVoxels<Vec3fTree, 1, false>, integrator/uniform/integrator.cu:309-311). Host-side: flattens

@@ -212,3 +212,58 @@ def test_device_edge_adjacency_equals_host_path(monkeypatch):
         assert np.array_equal(nd, nh) and np.array_equal(bits(bd), bits(bh)) and np.array_equal(bits(cd), bits(ch))
         for flip in (False, True):
             assert np.array_equal(bits(dev.silhouette(q, flip)), bits(host.silhouette(q, flip)))
+
+
+@pytest.mark.parametrize("name", ["star10k", "ico5", "soup2d_random", "soup3d_random", "two_triangles", "star_x4096"])
+def test_oriented_boxes_contain_their_subtrees(name):
+    """The traversal records carry one oriented box per child (csrc/lbvh.cuh: Obb) that only prunes: every vertex below a
+    child must project inside the child's intervals (fp64 check of the stored fp32 frame), the frame must be orthonormal
+    to rounding, and the intervals must be tight (exact extent of the projections + the 2^-20 max|coordinate| widening)."""
+    api = _api()
+    dim, v, p = _scene_cases()[name]
+    s = api.Scene(dim, v, p)
+    rec, lv = s.dump_traversal_layout()
+    n = len(p)
+    assert rec.shape == (n - 1, 24 if dim == 2 else 40)
+    refs = rec.view(np.uint32)[:, (8, 9) if dim == 2 else (12, 13)]
+    LEAF = np.uint32(0x80000000)
+    # leaf range of every child by a post-order walk over the child references
+    first = np.zeros((n - 1, 2), np.int64)
+    last = np.zeros((n - 1, 2), np.int64)
+    order, stack = [], [0]
+    while stack:
+        i = stack.pop()
+        order.append(i)
+        for r in refs[i]:
+            if not (r & LEAF):
+                stack.append(int(r))
+    for i in reversed(order):
+        for side in range(2):
+            r = refs[i, side]
+            if r & LEAF:
+                first[i, side] = last[i, side] = int(r & ~LEAF)
+            else:
+                first[i, side], last[i, side] = first[int(r)].min(), last[int(r)].max()
+    assert first[0].min() == 0 and last[0].max() == n - 1
+    M = float(np.abs(v[np.unique(p)]).max())
+    w = M * 2.0 ** -20
+    lv64 = lv.astype(np.float64)
+    rng = np.random.RandomState(3)
+    nodes = np.arange(n - 1) if n - 1 <= 4000 else np.unique(np.concatenate([np.arange(64), rng.randint(0, n - 1, 4000)]))
+    for i in nodes:
+        for side in range(2):
+            o = rec[i, (10 if dim == 2 else 16) + side * (6 if dim == 2 else 12):][: 6 if dim == 2 else 12].astype(np.float64)
+            pts = lv64[first[i, side]: last[i, side] + 1].reshape(-1, dim)
+            if dim == 2:
+                axes = np.array([[o[0], o[1]], [-o[1], o[0]]])
+                lo, hi = o[[2, 4]], o[[3, 5]]
+            else:
+                nrm, t = o[0:3], o[3:6]
+                axes = np.stack([nrm, t, np.cross(nrm, t)])
+                lo, hi = o[6:9], o[9:12]
+            np.testing.assert_allclose(axes @ axes.T, np.eye(dim), atol=2e-6)
+            pr = pts @ axes.T
+            assert np.all(pr >= lo - 1e-30) and np.all(pr <= hi + 1e-30), (name, i, side)
+            # tight: the interval is the extent of the projections plus the widening (and fp32 rounding of the projection)
+            slack = w + 4.0 * M * 2.0 ** -23
+            assert np.all(pr.min(0) - lo <= 2.0 * slack) and np.all(hi - pr.max(0) <= 2.0 * slack), (name, i, side)
