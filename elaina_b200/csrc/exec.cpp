@@ -214,12 +214,14 @@ namespace
         wost_scene *dir = nullptr, *neu = nullptr;
         wost_problem *prob = nullptr;
         wost_integrator *it = nullptr;
+        wost_comm *comm = nullptr; // non-null when started by torchrun / mpirun with more than one process (one per GPU)
         ~Handles()
         {
             wost_integrator_destroy(it);
             wost_problem_destroy(prob);
             wost_scene_destroy(dir);
             wost_scene_destroy(neu);
+            wost_comm_destroy(comm);
         }
     };
 
@@ -232,7 +234,16 @@ namespace
         const int dim = get(conf, "dimensionality").as_int();
         const std::string base = get(conf, "base_path").as_string(), exp = get(conf, "exp_name").as_string();
         const std::string out_dir = (base.empty() || base.back() == '/' ? base : base + "/") + exp;
+        // Multi-GPU (no counterpart in the reference, which is single-device): under torchrun / mpirun every process takes the
+        // GPU LOCAL_RANK, evaluates its interleaved row tiles of the frame, joins the gradient all-reduce of the guiding network,
+        // and rank 0 gathers the film and writes the outputs. A single process behaves exactly like the reference.
+        Handles H;
+        ck(wost_comm_create_from_env(&H.comm));
+        int rank = 0, world = 1;
+        wost_comm_info(H.comm, &rank, &world, nullptr);
+        const bool writer = rank == 0;
         mkdirs(out_dir);
+        if (writer)
         {
             std::string dumped;
             wjson::dump(conf, dumped, 4);
@@ -248,7 +259,6 @@ namespace
         if (type != "uniform" && type != "guided")
             fail(WOST_ERR_UNSUPPORTED, "Unrecognized integrator type.");
 
-        Handles H;
         // ---- Problem<DIM>::loadConfig
         wost_problem_desc d;
         memset(&d, 0, sizeof(d));
@@ -365,12 +375,14 @@ namespace
             s.max_guided_depth_training = get(setting, "maxGuidedDepthInTrainingPhase").as_int();
             s.max_guided_depth_guiding = get(setting, "maxGuidedDepthInGuidingPhase").as_int();
         }
+        ck(wost_comm_shard_settings(H.comm, &s, 4));
         ck(wost_integrator_create(H.prob, &s, guided ? WOST_GUIDED : WOST_UNIFORM, &H.it));
         if (guided)
         {
             std::string net;
             wjson::dump(get(conf, "network"), net, 0);
             ck(wost_reset_network(H.it, net.c_str()));
+            ck(wost_integrator_set_comm(H.it, H.comm));
         }
 
         // ---- channels (exec.cu:131-174)
@@ -388,7 +400,7 @@ namespace
         {
             std::string dir;
         } sink{out_dir};
-        if (s.save_spp_metrics_duration > 0 || s.save_time_metrics_duration > 0)
+        if (world == 1 && (s.save_spp_metrics_duration > 0 || s.save_time_metrics_duration > 0)) // progressive dumps: single process only
         {
             if (s.save_spp_metrics_duration > 0)
                 mkdirs(out_dir + "/frames");
@@ -422,11 +434,18 @@ namespace
             if (c == WOST_CH_SOLUTION)
             {
                 ck(wost_solve(H.it, &duration, &steps, &dev_ms));
+                ck(wost_film_gather(H.it, H.comm, WOST_CH_SOLUTION, 0));
+                double tmax[2] = {(double)duration, (double)dev_ms}, ssum[1] = {(double)steps};
+                ck(wost_comm_allreduce_f64(H.comm, tmax, 2, 1)); // whole-job numbers: time = max over ranks, walk-steps = sum
+                ck(wost_comm_allreduce_f64(H.comm, ssum, 1, 0));
+                duration = (uint64_t)tmax[0], dev_ms = (float)tmax[1], steps = (uint64_t)ssum[0];
                 solved = true;
             }
             else
                 ck(wost_render_channel(H.it, c));
         }
+        if (!writer)
+            return;
         if (guided && conf.number_or("print_network", 0) != 0)
         {
             float p[3] = {0.0f, dim == 3 ? -0.21f : 0.0f, 0.0f}, out[48];
@@ -495,6 +514,7 @@ namespace
             res.obj.emplace_back("duration", wjson::make_number((double)duration));
             res.obj.emplace_back("walk_steps", wjson::make_number((double)steps));
             res.obj.emplace_back("walk_steps_per_sec", wjson::make_number(dev_ms > 0 ? (double)steps / (dev_ms * 1e-3) : 0.0));
+            res.obj.emplace_back("n_gpus", wjson::make_number((double)world));
         }
         char ts[64];
         const time_t now = time(nullptr);

@@ -616,15 +616,21 @@ namespace wost
         t.cur = kInvalid;
         if (t.cur_d > t.best)
             return true;
-        const NodeViewE<D> n = load_tnode_e(bvh.tnodes + node);
+        const TNode<D> *rec = bvh.tnodes + node;
+        const NodeViewE<D> n = load_tnode_e(rec);
         const Box<D> lp = pad_box(n.le), rp = pad_box(n.re);
         const float Lmin = box_mindist(lp, q), Rmin = box_mindist(rp, q);
         const float Lmm = box_minmaxdist(lp, q), Rmm = box_minmaxdist(rp, q);
         bool goL = Lmin <= Rmm, goR = Rmin <= Lmm;
         if (!RefOrder)
         {
+            // restricted pass: only subtrees that can hold a leaf within thrW matter (exact extent, then oriented box)
             goL = goL && box_mindist(n.le, q) <= t.thr;
             goR = goR && box_mindist(n.re, q) <= t.thr;
+            if (goL)
+                goL = obb_mindist2(load_obb(rec, 0), q) <= t.thr;
+            if (goR)
+                goR = obb_mindist2(load_obb(rec, 1), q) <= t.thr;
         }
 #pragma unroll
         for (int side = 0; side < 2; ++side)
