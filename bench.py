@@ -143,7 +143,7 @@ def cpu_oracle_sample(wl, budget_s=12.0, nthreads=0, keep_field=False):
         t0 = time.perf_counter()
         sol, steps = orc.solve_uniform(prob, st, pixel_begin=r0 * W, pixel_end=(r0 + rows) * W, nthreads=cores)
         dt = time.perf_counter() - t0
-        if keep_field and first is None:
+        if keep_field:  # the last (largest) chunk is kept for the parity check
             first = (r0, r0 + rows, np.asarray(sol, np.float32).reshape(-1, 3)[r0 * W:(r0 + rows) * W].copy())
         total_steps += steps
         total_t += dt
@@ -233,8 +233,10 @@ def run_reference_arm(args, wl, rank, world):
 
 
 # ----------------------------------------------------------------------------------------------------------------------
-def issue_profile(dim, guided, walk_mode):
+def issue_profile(wl, guided, walk_mode):
     """issue-slot figures of the dominant kernel from the committed ncu capture of the same kernel (NOT measured in this run)"""
+    if guided or wl["name"] not in ("c3", "c3-small", "c5") or not walk_mode.startswith("persistent"):
+        return None  # the committed capture is of k_walk_persistent<2, lean variant> on the C3 geometry
     for name in ("traffic_r2.json", "traffic_r1d.json"):
         p = os.path.join(ROOT, "profiles", name)
         if not os.path.exists(p):
@@ -243,8 +245,6 @@ def issue_profile(dim, guided, walk_mode):
             tj = json.load(open(p))
         except Exception:
             continue
-        if guided or dim != 2 or not walk_mode.startswith("persistent"):
-            return None
         return tj
     return None
 
@@ -387,7 +387,7 @@ class Bench:
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "kernel": kernel, "bytes_per_walk_step": bps, "launches": int(kern_launches), "avg_launch_ms": kern_ms / max(1, kern_launches),
                 "kernel_share_of_step": kern_ms_max / dev_ms if dev_ms > 0 else None, "peak_source": peak_src}
-        ip = issue_profile(dim, guided, walk_mode)
+        ip = issue_profile(wl, guided, walk_mode)
         if ip is not None:
             roof["traffic"] = ip["dram_bytes_per_walk_step"] * steps_total / max(1, kern_launches)
             roof["traffic_source"] = "NOT measured in this run: DRAM bytes per walk-step of the committed ncu capture (%s) x this run's walk-steps per launch" % ip.get("source", "profiles/")

@@ -955,9 +955,10 @@ namespace wost
                 tc::tmem_ld16(lane_base + c43 + c16 * 16, v);
                 if (own43)
                 {
+                    // 128-bit reductions (red.global.add.v4.f32): 4x fewer atomics than one per weight
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        atomicAdd(g43 + c16 * 16 + j, v[j]);
+                    for (int j = 0; j < 16; j += 4)
+                        atomicAdd(reinterpret_cast<float4 *>(g43 + c16 * 16 + j), make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
                 }
             }
             if (r < 64)
@@ -968,8 +969,8 @@ namespace wost
                     float v[16];
                     tc::tmem_ld16(lane_base + kColG21 + c16 * 16, v);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        atomicAdd(a.grad + off1 + o * kHidden + c16 * 16 + j, v[j]);
+                    for (int j = 0; j < 16; j += 4)
+                        atomicAdd(reinterpret_cast<float4 *>(a.grad + off1 + o * kHidden + c16 * 16 + j), make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
                 }
             }
             else
@@ -980,8 +981,8 @@ namespace wost
                     float v[16];
                     tc::tmem_ld16(lane_base + kColG21 + kHidden + c16 * 16, v);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        atomicAdd(a.grad + o * K0 + c16 * 16 + j, v[j]);
+                    for (int j = 0; j < 16; j += 4)
+                        atomicAdd(reinterpret_cast<float4 *>(a.grad + o * K0 + c16 * 16 + j), make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
                 }
             }
         }

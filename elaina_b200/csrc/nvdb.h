@@ -7,8 +7,11 @@
 // Vec3f row of pnanovdb_grid_type_constants) and io/IO.h + NanoVDB.h:5817-5856 (FileHeader 16 B, FileMetaData 176 B + name).
 // The tree is flattened over its index bounding box: getValue() semantics (leaf values incl. inactive voxels, tile values of
 // childless table entries, background elsewhere), so that trilinear interpolation of the dense grid == the reference's
-// order-1 sampler. Supported: uncompressed files (Codec::NONE) and raw grid buffers, Vec3f grids, axis-aligned uniform
-// maps (the only kind a voxel size + origin can express), zero background (what lies outside the box reads as zero).
+// order-1 sampler. Supported: files written with Codec::NONE or Codec::ZIP (io/IO.h:221-236,279-292: a 64-bit compressed
+// size followed by one zlib stream that inflates to FileMetaData::gridSize bytes; inflated here with the system zlib) and raw
+// grid buffers; Vec3f grids, axis-aligned uniform maps (the only kind a voxel size + origin can express), zero background
+// (what lies outside the box reads as zero). Codec::BLOSC needs the blosc library, which this image does not have: such
+// files are reported as unsupported.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -16,6 +19,8 @@
 #include <cstring>
 #include <string>
 #include <vector>
+
+#include <zlib.h>
 
 namespace wnvdb
 {
@@ -100,20 +105,40 @@ namespace wnvdb
             const uint16_t grid_count = b.rd<uint16_t>(12), codec = b.rd<uint16_t>(14);
             if (grid_count == 0)
                 return "nvdb: file holds no grid";
-            if (codec != 0)
-                return "nvdb: compressed files (ZIP / BLOSC codec) are not supported, write with Codec::NONE";
+            if (codec > 1)
+                return "nvdb: compressed file with the BLOSC codec is not supported (no blosc library), write with Codec::NONE or Codec::ZIP";
             size_t pos = 16;
+            uint16_t first_codec = 0;
+            uint64_t first_grid_size = 0;
             for (uint16_t g = 0; g < grid_count; ++g)
             {
                 if (!b.ok(pos, 176))
                     return "nvdb: truncated metadata";
                 const uint32_t name_size = b.rd<uint32_t>(pos + 136); // FileMetaData::nameSize
                 const uint16_t gcodec = b.rd<uint16_t>(pos + 168);
-                if (gcodec != 0)
-                    return "nvdb: compressed grids are not supported, write with Codec::NONE";
+                if (gcodec > 1)
+                    return "nvdb: compressed grid with the BLOSC codec is not supported (no blosc library)";
+                if (g == 0)
+                    first_codec = gcodec, first_grid_size = b.rd<uint64_t>(pos); // FileMetaData::gridSize
                 pos += 176 + name_size;
             }
             grid = pos; // first grid of the first segment
+            if (first_codec == 1)
+            {
+                // Codec::ZIP (io/IO.h:279-292): uint64 size of the zlib stream, then the stream; inflates to gridSize bytes
+                if (!b.ok(grid, 8))
+                    return "nvdb: truncated compressed grid";
+                const uint64_t csize = b.rd<uint64_t>(grid);
+                if (!b.ok(grid + 8, (size_t)csize) || first_grid_size < 672 || first_grid_size > ((uint64_t)1 << 34))
+                    return "nvdb: truncated compressed grid";
+                std::vector<uint8_t> raw((size_t)first_grid_size);
+                uLongf n = (uLongf)raw.size();
+                if (uncompress(raw.data(), &n, bytes.data() + grid + 8, (uLong)csize) != Z_OK || (uint64_t)n != first_grid_size)
+                    return "nvdb: compressed grid does not inflate to its recorded size";
+                bytes.swap(raw);
+                b = Buf{bytes.data(), bytes.size()};
+                grid = 0;
+            }
         }
         else if (magic != kMagicGrid)
             return "nvdb: not a NanoVDB file (bad magic)";

@@ -2,8 +2,9 @@
 // Builds a small Vec3f NanoVDB grid with the reference's own NanoVDB headers, writes it uncompressed with
 // nanovdb::io::writeGrid, and samples it exactly like the reference's source stage does
 // (integrator/uniform/integrator.cu:309-311: worldToIndex + SampleFromVoxels<Vec3fTree, 1, false>).
-//   g++ -std=c++17 -O1 -I/root/reference/ext/openvdb/nanovdb tests/golden/make_nvdb_golden.cpp -o /tmp/make_nvdb_golden
-//   /tmp/make_nvdb_golden tests/golden/source_vec3f.nvdb tests/golden/source_vec3f_samples.txt
+//   g++ -std=c++17 -O1 -DNANOVDB_USE_ZIP -I/root/reference/ext/openvdb/nanovdb tests/golden/make_nvdb_golden.cpp -o /tmp/make_nvdb_golden -lz
+//   /tmp/make_nvdb_golden tests/golden/source_vec3f.nvdb tests/golden/source_vec3f_samples.txt tests/golden/source_vec3f_zip.nvdb
+// (the optional third argument writes the same grid with io::Codec::ZIP, the reference's zlib codec, io/IO.h:221-236)
 #include <nanovdb/NanoVDB.h>
 #include <nanovdb/io/IO.h>
 #include <nanovdb/math/SampleFromVoxels.h>
@@ -34,6 +35,8 @@ int main(int argc, char **argv)
             }
     auto handle = tools::createNanoGrid(grid);
     io::writeGrid(argv[1], handle, io::Codec::NONE);
+    if (argc > 3)
+        io::writeGrid(argv[3], handle, io::Codec::ZIP);
     const auto *g = handle.grid<Vec3f>();
     math::SampleFromVoxels<Vec3fTree, 1, false> sampler(g->tree());
     FILE *f = fopen(argv[2], "w");

@@ -50,6 +50,16 @@ def test_reader_reproduces_reference_samples():
     np.testing.assert_allclose(got, want, rtol=0, atol=3e-5)            # fp32 index arithmetic differs by rounding only
 
 
+def test_zip_codec_file_equals_uncompressed():
+    """Codec::ZIP (io/IO.h:221-236,279-292), fixture written by the reference's own NanoVDB headers built with NANOVDB_USE_ZIP
+    (tests/golden/make_nvdb_golden.cpp, third argument): the reader inflates it to the same dense grid as the Codec::NONE file."""
+    from elaina_b200 import scenes
+    a, oa, va = scenes.load_nvdb_source(NVDB)
+    b, ob, vb = scenes.load_nvdb_source(os.path.join(ROOT, "tests", "golden", "source_vec3f_zip.nvdb"))
+    assert a.shape == b.shape and oa == ob and va == vb
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
 def test_reader_errors_are_status_codes(tmp_path):
     from elaina_b200 import _lib, scenes
     with pytest.raises(_lib.WostError) as e:
@@ -61,12 +71,12 @@ def test_reader_errors_are_status_codes(tmp_path):
         scenes.load_nvdb_source(bad)
     assert "bad magic" in str(e.value)
     raw = bytearray(open(NVDB, "rb").read())
-    raw[14] = 1                                                          # FileHeader.codec = ZIP
-    z = tmp_path / "zip.nvdb"
+    raw[14] = 2                                                          # FileHeader.codec = BLOSC (no blosc library in this image)
+    z = tmp_path / "blosc.nvdb"
     z.write_bytes(bytes(raw))
     with pytest.raises(_lib.WostError) as e:
         scenes.load_nvdb_source(z)
-    assert "compressed" in str(e.value)
+    assert "BLOSC" in str(e.value)
     t = tmp_path / "trunc.nvdb"
     t.write_bytes(bytes(open(NVDB, "rb").read()[:5000]))
     with pytest.raises(_lib.WostError):
