@@ -499,7 +499,7 @@ def main():
                 sub.append(r)
 
     cpu, parity = None, None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:  # reported baseline: rank 0 at N = 1 only
         v, cores, sample, _, _, band = cpu_oracle_sample(wl, keep_field=True)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         if band is not None:

@@ -301,7 +301,7 @@ namespace wost
     WOST_DEV Vec<D> g_sample_direction(const WalkCtx<D> &c, const GArgs &a, const GItem<D> &it, const float *raw, float &pdf)
     {
         const WalkState<D> &w = it.w;
-        const float p_sel = dm_logistic(raw[kLobes * (D + 2)]);
+        const float p_sel = g_logistic(raw[kLobes * (D + 2)]);
         const bool inside = aabb_contains<D>(c.aabb_min, c.aabb_max, w.x);
         const Philox4 qs = wost_rng(c.seed, w.pixel, w.sample, a.depth, WOST_RNG_SELECT, 0);
         // uniformSamplingFraction is only ever compared with 0 and 1 by the reference (:514, :1034): 0 = always guided,
@@ -350,6 +350,7 @@ namespace wost
         return dir;
     }
 
+    constexpr int kBounceStackLevels = 12;
     // ---- one guided bounce
     template <int D, int K0>
     __global__ void __launch_bounds__(kGBlock) k_g_bounce(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a, const __grid_constant__ GuideNetView net)
@@ -357,9 +358,11 @@ namespace wost
         extern __shared__ __align__(1024) char smem_raw[];
         SmemStack st;
         uint2 spill_mem[kSpillLevels];
-        st.init(reinterpret_cast<uint2 *>(smem_raw), a.overflow, spill_mem);
+        // the bounce kernel only traverses for the ray cast against the Neumann mesh: a 12-level shared stack (deeper levels
+        // spill) keeps the CTA at 55 KB of shared memory -> 4 CTAs per SM instead of 3 (the kernel is latency-bound)
+        st.init(reinterpret_cast<uint2 *>(smem_raw), a.overflow, spill_mem, kBounceStackLevels);
         MlpFwdSmem<K0> sm;
-        sm.carve(smem_raw + (size_t)kGBlock * kSmemLevels * sizeof(uint2));
+        sm.carve(smem_raw + (size_t)kGBlock * kBounceStackLevels * sizeof(uint2));
         __shared__ int s_tile;
         const bool fused = a.precomputed == nullptr;
         uint32_t tmem_base = 0, phase = 0;
@@ -1232,7 +1235,7 @@ namespace wost
     template <int D, int K0>
     static void launch_bounce(wost_integrator *it, const WalkCtx<D> &ctx, const GArgs &a, int grid)
     {
-        const size_t smem = stack_smem_bytes(kGBlock) + MlpFwdSmem<K0>::kBytes;
+        const size_t smem = stack_smem_bytes(kGBlock, kBounceStackLevels) + MlpFwdSmem<K0>::kBytes;
         static bool attr_done = false; // per instantiation
         if (!attr_done)
         {
@@ -1244,7 +1247,7 @@ namespace wost
     template <int D, int K0>
     static int bounce_grid()
     {
-        const size_t smem = stack_smem_bytes(kGBlock) + MlpFwdSmem<K0>::kBytes;
+        const size_t smem = stack_smem_bytes(kGBlock, kBounceStackLevels) + MlpFwdSmem<K0>::kBytes;
         cudaFuncSetAttribute(k_g_bounce<D, K0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         int occ = 1;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_bounce<D, K0>, kGBlock, smem) != cudaSuccess)
@@ -1381,6 +1384,16 @@ namespace wost
         WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_g_arrive<D, false, F>, kGBlock, stack_smem));
         const int grid_full = sm_count() * std::max(1, occ);
         int grid_bounce = sm_count();
+        // Launches over few items (training batches: one sample per pixel) leave ~2 items per resident lane: the persistent lanes
+        // run out of refills early and the launch ends in a long tail of sparsely filled warps. Fewer, longer-lived lanes
+        // (>= items_per_lane items each) trade latency hiding for a shorter tail.
+        static const int items_per_lane = []
+        {
+            const char *e = getenv("WOST_G_ITEMS_PER_LANE");
+            return e ? std::max(1, atoi(e)) : 1;
+        }();
+        auto grid_for = [&](long long max_items)
+        { return (int)std::max<long long>(sm_count(), std::min<long long>(grid_full, (max_items + (long long)kGBlock * items_per_lane - 1) / ((long long)kGBlock * items_per_lane))); };
         WOST_DISPATCH_K0(D, n.k0, (grid_bounce = bounce_grid<D, K0_>()));
         const int max_train_depth = std::min(kMaxTrainDepth, it->s.max_train_depth > 0 ? it->s.max_train_depth : 3);
 
@@ -1505,7 +1518,7 @@ namespace wost
                     a.in = queue(d & 1), a.out = queue((d + 1) & 1);
                     a.in_count = counts + d, a.out_count = counts + d + 1, a.cursor = cur_a + d + 1, a.depth = (uint32_t)(d + 1);
                     prof_mark(0);
-                    k_g_arrive<D, false, F><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
+                    k_g_arrive<D, false, F><<<grid_for((long long)it->n_active * Sb), kGBlock, stack_smem, st>>>(ctx, a);
                     ++it->launches, ++it->step_launches;
                 }
             }
@@ -1514,7 +1527,7 @@ namespace wost
                 a.in = queue(G & 1), a.out = queue((G + 1) & 1);
                 a.in_count = counts + G, a.out_count = nullptr, a.cursor = cur_b + G, a.depth = (uint32_t)G;
                 prof_mark(2);
-                k_g_finish<D, F><<<grid_full, kGBlock, stack_smem, st>>>(ctx, a);
+                k_g_finish<D, F><<<grid_for((long long)it->n_active * Sb), kGBlock, stack_smem, st>>>(ctx, a);
                 ++it->launches, ++it->step_launches;
             }
             prof_mark(3);

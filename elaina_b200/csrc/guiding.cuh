@@ -105,7 +105,7 @@ namespace wost
                     stride *= res;
                 }
             }
-            c.idx[corner] = g.off[level] + index % size;
+            c.idx[corner] = g.off[level] + (index < size ? index : index % size); // dense levels never wrap: keep the integer division off the hot path
             c.w[corner] = w;
         }
     }

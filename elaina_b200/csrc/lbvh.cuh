@@ -328,11 +328,13 @@ namespace wost
         uint2 *base; // column of this thread (already offset by tid)
         int stride;  // blockDim.x
         int sp;
+        int levels; // entries of this stack that live in shared memory (kSmemLevels unless the kernel asked for fewer)
         int *overflow; // [0] stack overflow flag, [1] full reference-order traversals, [2] restricted second passes (statistics)
         uint2 *spill; // kSpillLevels entries of thread-local memory owned by the kernel (kept outside this struct so that the
                       // struct itself -- sp, base -- stays in registers)
-        WOST_DEV void init(uint2 *smem, int *overflow_flag, uint2 *spill_mem)
+        WOST_DEV void init(uint2 *smem, int *overflow_flag, uint2 *spill_mem, int smem_levels = kSmemLevels)
         {
+            levels = smem_levels;
             spill = spill_mem;
             base = smem + threadIdx.x;
             stride = blockDim.x;
@@ -342,10 +344,10 @@ namespace wost
         WOST_DEV void push(uint32_t ref, float d)
         {
             const uint2 e = make_uint2(ref, __float_as_uint(d));
-            if (__builtin_expect(sp < kSmemLevels, 1))
+            if (__builtin_expect(sp < levels, 1))
                 base[sp * stride] = e;
-            else if (sp < kSmemLevels + kSpillLevels)
-                spill_store(spill, sp - kSmemLevels, e);
+            else if (sp < levels + kSpillLevels)
+                spill_store(spill, sp - levels, e);
             else
             {
                 if (overflow)
@@ -358,10 +360,10 @@ namespace wost
         {
             --sp;
             uint2 e;
-            if (__builtin_expect(sp < kSmemLevels, 1))
+            if (__builtin_expect(sp < levels, 1))
                 e = base[sp * stride];
             else
-                e = spill_load(spill, sp - kSmemLevels);
+                e = spill_load(spill, sp - levels);
             StackEntry r;
             r.ref = e.x;
             r.d = __uint_as_float(e.y);
@@ -369,7 +371,7 @@ namespace wost
         }
         WOST_DEV bool empty() const { return sp <= 0; }
     };
-    inline size_t stack_smem_bytes(int block_threads) { return (size_t)block_threads * kSmemLevels * sizeof(uint2); }
+    inline size_t stack_smem_bytes(int block_threads, int levels = kSmemLevels) { return (size_t)block_threads * levels * sizeof(uint2); }
 
     // ---------------------------------------------------------------- closest primitive (core/query.cuh:238-318)
     // The closest-point traversal is RESUMABLE: nearest_begin() sets up the per-lane state, nearest_trip() opens one

@@ -3,11 +3,19 @@
 //
 // Follows integrator/guided/distribution.h:136-444 (VMM<2|3,8>), util/vonmises.h:64-209, util/vmf.h:21-84 and the
 // output activations of integrator/guided/train.h:49-105. Differences, all stated here:
-//   * fp32 transcendentals come from detmath.h (same bits on host and device);
-//   * the Best-Fisher rejection sampler of the von Mises lobe keeps the reference's double arithmetic
-//     (util/vonmises.h:95-118: the proposal parameter r = 1 + O(1/kappa) is not representable in fp32 for the
-//     kappa <= e^15 the activation allows) but draws its numbers from the counter-based Philox stream with the
-//     rejection iteration as a counter word, and gives up after 64 iterations (the reference loops forever);
+//   * fp32 transcendentals: on the device the hardware approximations (ex2 / lg2 / rcp based __expf, __logf, __fdividef,
+//     rsqrtf) -- what the reference's own --use_fast_math build executes (CMakeLists.txt:64-70); host compiles of this header
+//     use detmath.h. The guided layer is compared statistically and at stated tolerances, never bit for bit;
+//   * the von Mises density is evaluated as exp(kappa (cos - 1) + [kappa - log I0(kappa)] - log 2 pi) with the bracket formed
+//     without cancellation (0.5 log kappa - log(poly) for kappa >= 3.75): the reference's kappa cos - log 2 pi - log I0(kappa)
+//     loses |kappa| ulps to cancellation (kappa reaches e^15); same value up to that rounding noise, and the per-lobe
+//     normalisers are computed once per decode instead of once per density evaluation;
+//   * the Best-Fisher rejection sampler of the von Mises lobe keeps the reference's double arithmetic for the proposal
+//     parameter r = 1 + O(1/kappa), the candidate f and the acceptance variable c (util/vonmises.h:95-118: not representable in
+//     fp32 for the kappa <= e^15 the activation allows); cos(pi u), the logarithm of the acceptance test and the final arc
+//     cosine (written 2 asin(sqrt((1 -+ f) / 2)), exact near f = +-1) run in fp32 -- they only perturb the proposal draw / the
+//     acceptance boundary at the 1e-7 level. Numbers come from the counter-based Philox stream with the rejection iteration as a
+//     counter word; the loop gives up after 64 iterations (the reference loops forever);
 //   * d log I0 / d kappa is written as the Horner derivative of the same polynomials instead of the reference's
 //     expanded expression (util/vonmises.h:135-170) -- algebraically identical.
 #pragma once
@@ -27,6 +35,41 @@ namespace wost
         static constexpr int kOut = kLobes * kLobeDims + 1;       // + selection probability (33 / 41)
         static constexpr int kOutPadded = 48;                     // parameters.h:25,36
     };
+
+    // ---- transcendental / division flavour of the guided layer (see the header comment)
+    WOST_HOSTDEV float g_exp(float x)
+    {
+#if defined(__CUDA_ARCH__)
+        return __expf(x);
+#else
+        return dm_exp(x);
+#endif
+    }
+    WOST_HOSTDEV float g_log(float x)
+    {
+#if defined(__CUDA_ARCH__)
+        return __logf(x);
+#else
+        return dm_log(x);
+#endif
+    }
+    WOST_HOSTDEV float g_div(float a, float b)
+    {
+#if defined(__CUDA_ARCH__)
+        return __fdividef(a, b);
+#else
+        return dm_div(a, b);
+#endif
+    }
+    WOST_HOSTDEV float g_logistic(float x) { return g_div(1.0f, 1.0f + g_exp(-x)); }
+    WOST_HOSTDEV float g_rsqrt(float x)
+    {
+#if defined(__CUDA_ARCH__)
+        return rsqrtf(x);
+#else
+        return dm_div(1.0f, dm_sqrt(x));
+#endif
+    }
 
     // ---- Abramowitz-Stegun polynomials of log I0 (util/vonmises.h:18-92)
     WOST_HOSTDEV float i0_small_poly(float y, float *dy)
@@ -62,54 +105,76 @@ namespace wost
     {
         if (x < 3.75f)
         {
-            float y = dm_div(x, 3.75f);
+            float y = g_div(x, 3.75f);
             y *= y;
-            return dm_log(i0_small_poly(y, nullptr));
+            return g_log(i0_small_poly(y, nullptr));
         }
-        const float y = dm_div(3.75f, x);
-        return x - 0.5f * dm_log(x) + dm_log(i0_large_poly(y, nullptr));
+        const float y = g_div(3.75f, x);
+        return x - 0.5f * g_log(x) + g_log(i0_large_poly(y, nullptr));
+    }
+    // kappa - log I0(kappa) - log(2 pi): the log-normaliser of the von Mises density written around cos - 1, no cancellation
+    WOST_HOSTDEV float vm_lognorm(float x)
+    {
+        if (x < 3.75f)
+        {
+            float y = x * (1.0f / 3.75f);
+            y *= y;
+            return x - g_log(i0_small_poly(y, nullptr)) - 1.8378770664093453f;
+        }
+        const float y = g_div(3.75f, x);
+        return 0.5f * g_log(x) - g_log(i0_large_poly(y, nullptr)) - 1.8378770664093453f;
     }
     // d/dkappa log I0(kappa)
     WOST_HOSTDEV float dlog_bessel_i0(float x)
     {
         if (x < 3.75f)
         {
-            const float t = dm_div(x, 3.75f);
+            const float t = g_div(x, 3.75f);
             float d;
             const float p = i0_small_poly(t * t, &d);
-            return dm_div(d, p) * dm_div(2.0f * x, 3.75f * 3.75f);
+            return g_div(d, p) * g_div(2.0f * x, 3.75f * 3.75f);
         }
-        const float y = dm_div(3.75f, x);
+        const float y = g_div(3.75f, x);
         float d;
         const float p = i0_large_poly(y, &d);
-        return 1.0f - dm_div(0.5f, x) - dm_div(d, p) * dm_div(y, x);
+        return 1.0f - g_div(0.5f, x) - g_div(d, p) * g_div(y, x);
     }
     // VonMises::eval / d_eval_d_kappa (util/vonmises.h:128-183)
+    WOST_HOSTDEV float vm_eval_ln(float kappa, float lognorm, float cosTheta)
+    {
+        return (kappa < 1e-3f) ? kInv2Pi : g_exp(kappa * (cosTheta - 1.0f) + lognorm);
+    }
     WOST_HOSTDEV float vm_eval(float kappa, float cosTheta)
     {
         if (kappa < 1e-3f)
             return kInv2Pi;
-        return dm_exp(kappa * cosTheta - 1.8378770664093453f - log_bessel_i0(kappa)); // log(2 pi)
+        return vm_eval_ln(kappa, vm_lognorm(kappa), cosTheta);
     }
     WOST_HOSTDEV float vm_deval_dkappa(float kappa, float cosTheta)
     {
         return vm_eval(kappa, cosTheta) * (cosTheta - dlog_bessel_i0(kappa));
     }
-    // VMF::eval (util/vmf.h:27-32)
+    // VMF::eval (util/vmf.h:27-32): exp(kappa min(0, cos - 1)) * kappa / (2 pi (1 - exp(-2 kappa)))
+    WOST_HOSTDEV float vmf_norm(float kappa) { return g_div(kappa, DM_2PI * (1.0f - g_exp(-2.0f * kappa))); }
+    WOST_HOSTDEV float vmf_eval_n(float kappa, float norm, float cosTheta)
+    {
+        return (kappa < kMEps) ? kInv4Pi : g_exp(kappa * fmin_nn(0.0f, cosTheta - 1.0f)) * norm;
+    }
     WOST_HOSTDEV float vmf_eval(float kappa, float cosTheta)
     {
         if (kappa < kMEps)
             return kInv4Pi;
-        return dm_div(dm_exp(kappa * fmin_nn(0.0f, cosTheta - 1.0f)) * kappa, DM_2PI * (1.0f - dm_exp(-2.0f * kappa)));
+        return vmf_eval_n(kappa, vmf_norm(kappa), cosTheta);
     }
 
     // ---- activations (train.h:49-105)
-    WOST_HOSTDEV float act_exp(float v) { return dm_exp(fmin_nn(fmax_nn(v, -10.0f), 15.0f)); }
+    WOST_HOSTDEV float act_exp(float v) { return g_exp(fmin_nn(fmax_nn(v, -10.0f), 15.0f)); }
 
     template <int D>
     struct VMM
     {
         float lambda[kLobes], kappa[kLobes], weight[kLobes];
+        float norm[kLobes]; // 2D: log-normaliser kappa - log I0(kappa) - log 2 pi; 3D: kappa / (2 pi (1 - exp(-2 kappa)))
         Vec<D> mu[kLobes], mu_orig[kLobes];
         float total;
 
@@ -123,6 +188,7 @@ namespace wost
                 const float *p = raw + i * (D + 2);
                 lambda[i] = act_exp(p[0]);
                 kappa[i] = act_exp(p[1]);
+                norm[i] = (D == 2) ? vm_lognorm(kappa[i]) : vmf_norm(kappa[i]);
                 float n2 = 0.0f;
 #pragma unroll
                 for (int k = 0; k < D; ++k)
@@ -130,20 +196,21 @@ namespace wost
                     mu_orig[i][k] = p[2 + k];
                     n2 += p[2 + k] * p[2 + k];
                 }
-                const float n = dm_sqrt(n2);
+                const float inv = (n2 > 0.0f) ? g_rsqrt(n2) : 1.0f; // Eigen normalized(): x / norm when norm > 0
 #pragma unroll
                 for (int k = 0; k < D; ++k)
-                    mu[i][k] = (n > 0.0f) ? dm_div(mu_orig[i][k], n) : mu_orig[i][k]; // Eigen normalized(): x / norm when norm > 0
+                    mu[i][k] = mu_orig[i][k] * inv;
                 total += lambda[i];
             }
+            const float inv_total = g_div(1.0f, total);
 #pragma unroll
             for (int i = 0; i < kLobes; ++i)
-                weight[i] = dm_div(lambda[i], total);
+                weight[i] = lambda[i] * inv_total;
         }
         WOST_HOSTDEV float lobe_pdf(int i, const Vec<D> &w) const
         {
             const float c = vdot(w, mu[i]);
-            return D == 2 ? vm_eval(kappa[i], c) : vmf_eval(kappa[i], c);
+            return D == 2 ? vm_eval_ln(kappa[i], norm[i], c) : vmf_eval_n(kappa[i], norm[i], c);
         }
         WOST_HOSTDEV float pdf(const Vec<D> &w) const
         {
@@ -206,14 +273,32 @@ namespace wost
                 const Philox4 q = wost_rng(seed, pixel, sample, depth, WOST_RNG_GUIDED, it);
                 const double u1 = u64_to_unit_double(q.x, q.y), u2 = u64_to_unit_double(q.z, q.w);
                 sgn = (q.w & 1u) ? 1.0 : -1.0;
+#if defined(__CUDA_ARCH__)
+                const double z = (double)cospif((float)u1);
+#else
                 const double z = cos(3.14159265358979323846 * u1);
+#endif
                 f = (1.0 + pr * z) / (pr + z);
                 const double c = k * (pr - f);
-                if ((c * (2.0 - c) - u2) > 0.0 || (log(c / u2) + 1.0 - c >= 0.0))
+                if ((c * (2.0 - c) - u2) > 0.0)
                     break;
+#if defined(__CUDA_ARCH__)
+                if (__logf((float)c) - __logf((float)u2) + 1.0f - (float)c >= 0.0f)
+                    break;
+#else
+                if (log(c / u2) + 1.0 - c >= 0.0)
+                    break;
+#endif
             }
             f = f > 1.0 ? 1.0 : (f < -1.0 ? -1.0 : f);
+#if defined(__CUDA_ARCH__)
+            // acos(f) = 2 asin(sqrt((1 - f) / 2)) for f >= 0, pi - 2 asin(sqrt((1 + f) / 2)) below: 1 -+ f is formed in double
+            const float half = (float)((f >= 0.0 ? 1.0 - f : 1.0 + f) * 0.5);
+            const float a = 2.0f * asinf(sqrtf(half));
+            theta = (float)sgn * (f >= 0.0 ? a : 3.14159265358979323846f - a);
+#else
             theta = (float)(sgn * acos(f));
+#endif
         }
         float s, c;
         dm_sincos(theta, &s, &c);
@@ -233,11 +318,11 @@ namespace wost
         Vec<3> t = vcross(n, a);
         float l = vlen(t);
         if (l > 0.0f)
-            t[0] = dm_div(t[0], l), t[1] = dm_div(t[1], l), t[2] = dm_div(t[2], l);
+            t[0] = g_div(t[0], l), t[1] = g_div(t[1], l), t[2] = g_div(t[2], l);
         Vec<3> b = vcross(n, t);
         l = vlen(b);
         if (l > 0.0f)
-            b[0] = dm_div(b[0], l), b[1] = dm_div(b[1], l), b[2] = dm_div(b[2], l);
+            b[0] = g_div(b[0], l), b[1] = g_div(b[1], l), b[2] = g_div(b[2], l);
         Vec<3> r;
 #pragma unroll
         for (int k = 0; k < 3; ++k)
@@ -260,7 +345,7 @@ namespace wost
             return l; // uniformSampleSphere: not rotated (vmf.h:46-47)
         }
         // cosTheta = 1 + log1p(-u + exp(-2k) u) / k ; log1p(x) evaluated as log(1 + x) on the detmath log
-        const float cosT = 1.0f + dm_div(dm_log(1.0f + (-u0 + dm_exp(-2.0f * kappa) * u0)), kappa);
+        const float cosT = 1.0f + g_div(g_log(1.0f + (-u0 + g_exp(-2.0f * kappa) * u0)), kappa);
         const float sinT = dm_sqrt(fmax_nn(0.0f, 1.0f - cosT * cosT));
         float s, c;
         dm_sincos(DM_2PI * u1, &s, &c);
@@ -301,14 +386,14 @@ namespace wost
         {
             float *g = grad + sg * (D + 2);
             const float lambda = m.lambda[sg], kappa = m.kappa[sg], w = m.weight[sg];
-            float dl = dm_div((p[sg] + pr[sg]) * (m.total - lambda), m.total * m.total);
+            float dl = g_div((p[sg] + pr[sg]) * (m.total - lambda), m.total * m.total);
 #pragma unroll
             for (int k = 0; k < kLobes; ++k)
                 if (k != sg)
                 {
-                    dl -= dm_div(m.weight[k], m.total) * p[k];
+                    dl -= g_div(m.weight[k], m.total) * p[k];
                     if (onN)
-                        dl -= dm_div(m.weight[k], m.total) * pr[k];
+                        dl -= g_div(m.weight[k], m.total) * pr[k];
                 }
             g[0] = dl;
             float n2 = 0.0f;
@@ -325,12 +410,12 @@ namespace wost
                     dk += w * vm_deval_dkappa(kappa, vdot(wr, m.mu[sg]));
                 g[1] = dk;
                 const float mx = m.mu_orig[sg][0], my = m.mu_orig[sg][1];
-                float dx = dm_div(w * p[sg] * kappa * my * (-mx * wi[1] + my * wi[0]), denom);
-                float dy = dm_div(w * p[sg] * kappa * mx * (mx * wi[1] - my * wi[0]), denom);
+                float dx = g_div(w * p[sg] * kappa * my * (-mx * wi[1] + my * wi[0]), denom);
+                float dy = g_div(w * p[sg] * kappa * mx * (mx * wi[1] - my * wi[0]), denom);
                 if (onN)
                 {
-                    dx += dm_div(w * pr[sg] * kappa * my * (-mx * wr[1] + my * wr[0]), denom);
-                    dy += dm_div(w * pr[sg] * kappa * mx * (mx * wr[1] - my * wr[0]), denom);
+                    dx += g_div(w * pr[sg] * kappa * my * (-mx * wr[1] + my * wr[0]), denom);
+                    dy += g_div(w * pr[sg] * kappa * mx * (mx * wr[1] - my * wr[0]), denom);
                 }
                 g[2] = dx;
                 g[3] = dy;
@@ -342,8 +427,8 @@ namespace wost
                     ik = 0.000962f + -0.344883f * kappa + 0.030147f * kappa * kappa;
                 else
                 {
-                    const float e = dm_exp(-2.0f * kappa);
-                    ik = dm_div(1.0f, kappa) - dm_div(1.0f + e, 1.0f - e);
+                    const float e = g_exp(-2.0f * kappa);
+                    ik = g_div(1.0f, kappa) - g_div(1.0f + e, 1.0f - e);
                 }
                 float dk = w * p[sg] * (vdot(wi, m.mu[sg]) + ik);
                 if (onN)
@@ -359,9 +444,9 @@ namespace wost
                     const Vec<D> &v = pass == 0 ? wi : wr;
                     const float pv = pass == 0 ? p[sg] : pr[sg];
                     const float x = v[0], y = v[1], z = v[D - 1];
-                    const float gx = dm_div(w * pv * kappa * (-mx * my * y - mx * mz * z + my * my * x + mz * mz * x), denom);
-                    const float gy = dm_div(w * pv * kappa * (-mx * my * x - my * mz * z + mx * mx * y + mz * mz * y), denom);
-                    const float gz = dm_div(w * pv * kappa * (-mx * mz * x - my * mz * y + mx * mx * z + my * my * z), denom);
+                    const float gx = g_div(w * pv * kappa * (-mx * my * y - mx * mz * z + my * my * x + mz * mz * x), denom);
+                    const float gy = g_div(w * pv * kappa * (-mx * my * x - my * mz * z + mx * mx * y + mz * mz * y), denom);
+                    const float gz = g_div(w * pv * kappa * (-mx * mz * x - my * mz * y + mx * mx * z + my * my * z), denom);
                     if (pass == 0)
                         g[2] = gx, g[3] = gy, g[D + 1] = gz;
                     else
@@ -389,7 +474,7 @@ namespace wost
         m.decode(raw);
         const float dirPdf = t.dirPdf + kMEps;
         const float guidePdf = vmm_grad_prob(m, t.dir, t.onN, t.nN, dl) + kMEps;
-        const float prefix = dm_div(dm_div(-t.Li, dirPdf), guidePdf) * loss_scale_over_n;
+        const float prefix = g_div(g_div(-t.Li, dirPdf), guidePdf) * loss_scale_over_n;
 #pragma unroll
         for (int sg = 0; sg < kLobes; ++sg)
         {
@@ -402,9 +487,9 @@ namespace wost
             for (int k = 0; k < D; ++k)
                 g[2 + k] = prefix * g[2 + k];
         }
-        const float sp = dm_logistic(raw[kLobes * (D + 2)]);
+        const float sp = g_logistic(raw[kLobes * (D + 2)]);
         const float up = t.onN ? (D == 2 ? 1.0f / DM_PI : 1.0f / DM_2PI) : (D == 2 ? 1.0f / DM_2PI : 1.0f / DM_4PI);
-        dl[kLobes * (D + 2)] = dm_div(loss_scale_over_n * -0.2f * t.Li * (guidePdf - up), dirPdf * dirPdf) * (sp * (1.0f - sp));
-        return dm_div(-t.Li, dirPdf) * dm_log(guidePdf);
+        dl[kLobes * (D + 2)] = g_div(loss_scale_over_n * -0.2f * t.Li * (guidePdf - up), dirPdf * dirPdf) * (sp * (1.0f - sp));
+        return g_div(-t.Li, dirPdf) * g_log(guidePdf);
     }
 } // namespace wost
