@@ -108,6 +108,7 @@ namespace wost
         int *rec_count;
         float *total;
         const float *precomputed; // validation mode: raw outputs [item][48] from k_g_mlp_simt, else nullptr
+        int refill;               // lanes that must be waiting before the warp runs a tail phase (see default_refill_threshold)
     };
 
     // closest-point query + separate / boundary / source / Neumann stages of the point the walk has just reached.
@@ -185,7 +186,6 @@ namespace wost
     // neighbouring items; lock-step traversal (one item per lane per round) left 7 of 32 lanes busy
     // (profiles/r1_notes.md), refilling keeps the traversal -- the bulk of the instructions -- near full width.
     // First: items are synthesised from (pixel, sample) = generateEvaluationPointsImpl (integrator.cu:131-151).
-    constexpr int kGRefill = 6;
     // lean 3D variants are compiled for 8 CTAs/SM like k_walk_persistent (integrator.cu: persist_min_ctas); 0 = compiler's budget
     constexpr int g_min_ctas(int D, int F) { return (D == 3 && !(F & kFeatNeumann)) ? 8 : 0; }
     template <int D, bool First, int F>
@@ -211,7 +211,7 @@ namespace wost
         {
             const unsigned trav_mask = __ballot_sync(kFullMask, trav);
             const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has || !exhausted));
-            if (pend_mask != 0u && (__popc(pend_mask) >= kGRefill || trav_mask == 0u))
+            if (pend_mask != 0u && (__popc(pend_mask) >= a.refill || trav_mask == 0u))
             {
                 bool on = false;
                 if (!trav && has)
@@ -457,7 +457,7 @@ namespace wost
         {
             const unsigned trav_mask = __ballot_sync(kFullMask, trav);
             const unsigned pend_mask = __ballot_sync(kFullMask, !trav && (has || !exhausted));
-            if (pend_mask != 0u && (__popc(pend_mask) >= kGRefill || trav_mask == 0u))
+            if (pend_mask != 0u && (__popc(pend_mask) >= a.refill || trav_mask == 0u))
             {
                 if (!trav && has && need_contrib)
                 {
@@ -1482,6 +1482,7 @@ namespace wost
             for (int j = 0; j < Sb; ++j)
                 ++it->slot_n[(size_t)(a.slot0 + j)];
             a.training = training ? 1 : 0;
+            a.refill = default_refill_threshold(D, F);
             a.max_train_depth = max_train_depth;
             a.uniform_fraction = ufrac;
             a.rec = g.rec.ptr, a.rec_onN = g.rec_onN.ptr, a.rec_count = g.rec_count.ptr, a.total = g.total.ptr;

@@ -151,7 +151,7 @@ namespace wost
     // Persistent walk kernel (default mode): ONE launch per batch of S samples-per-pixel. Each lane owns a whole walk
     // -- state in registers from the evaluation point to the epsilon-shell -- and the warp runs a two-phase loop:
     //   traversal trips   every lane with a closest-point query in flight opens one node / evaluates one leaf;
-    //   tail + refill     as soon as kRefillThreshold lanes have finished their query (or nobody is traversing any
+    //   tail + refill     as soon as refill_threshold lanes (walk.cuh: default_refill_threshold) have finished their query (or nobody is traversing any
     //                     more) those lanes run the rest of their walk step (walk_step_tail: epsilon-shell test,
     //                     Dirichlet read-out, silhouette query, source / Neumann samples, direction sample + ray),
     //                     lanes whose walk ended claim new (pixel, sample) jobs with one atomic per warp, and all of
@@ -160,7 +160,6 @@ namespace wost
     // number of visits per query varies 10x between neighbouring lanes, and a bounce costs neither a kernel launch nor a
     // queue round trip through HBM. Same Philox stream (pixel, sample, depth) and same per-(slot, pixel) accumulators
     // as the wavefront kernel, hence the same film bit for bit.
-    constexpr int kRefillThreshold = 6;
 
     struct PersistArgs
     {
@@ -607,9 +606,7 @@ namespace wost
         int occ = 1;
         WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_walk_persistent<D, RefOrder, F>, kWalkBlock, smem));
         const int grid_full = sm_count() * std::max(1, occ);
-        int refill_threshold = kRefillThreshold;
-        if (const char *e = getenv("WOST_REFILL_THRESHOLD")) // tuning knob (profiles/r1_notes.md)
-            refill_threshold = std::max(1, std::min(32, atoi(e)));
+        const int refill_threshold = default_refill_threshold(D, F);
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_acc.ptr, 0, sizeof(float4) * (size_t)S * std::max(1, it->n_active), st));
         WOST_CUDA_TRY(cudaMemsetAsync(it->d_steps.ptr, 0, sizeof(unsigned long long), st));
         it->launches = 0;

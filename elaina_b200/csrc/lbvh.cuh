@@ -910,13 +910,16 @@ namespace wost
             have = false;
             if (node_d > best * best)
                 continue;
-            const NodeView<D> n = load_tnode(bvh.tnodes + node);
+            const TNode<D> *rec = bvh.tnodes + node;
+            const NodeView<D> n = load_tnode(rec);
             Cone<D> lc, rc;
             load_cnode(bvh.cnodes + node, lc, rc);
             const float Lmin = box_mindist(n.lb, q), Rmin = box_mindist(n.rb, q);
             const float best2 = best * best;
-            const bool hitL = lc.half_angle >= 0.0f && Lmin <= best2 && cone_overlap(lc, q, n.lb, Lmin);
-            const bool hitR = rc.half_angle >= 0.0f && Rmin <= best2 && cone_overlap(rc, q, n.rb, Rmin);
+            // a child whose oriented box (a lower bound of the distance to every vertex and edge below it) lies beyond the running
+            // minimum cannot improve it: skipped before its cone test (pruning only, like the closest-point query)
+            const bool hitL = lc.half_angle >= 0.0f && Lmin <= best2 && obb_mindist2(load_obb(rec, 0), q) <= best2 && cone_overlap(lc, q, n.lb, Lmin);
+            const bool hitR = rc.half_angle >= 0.0f && Rmin <= best2 && obb_mindist2(load_obb(rec, 1), q) <= best2 && cone_overlap(rc, q, n.rb, Rmin);
             bool pushL = false;
             if (hitL)
             {

@@ -8,6 +8,8 @@
 // Semantics (what is computed, in which order contributions reach the pixel accumulator) follow the reference stage
 // by stage; file:line cited at each block. Randomness is the counter-based Philox stream of philox.h.
 #pragma once
+#include <algorithm>
+#include <cstdlib>
 #include "lbvh.cuh"
 #include "philox.h"
 #include "problem.cuh"
@@ -542,6 +544,22 @@ namespace wost
     }
     // One step of the UNIFORM integrator. Returns true when the walk goes on (w holds the next evaluation point).
     // Warp-synchronous (the closest-point driver is): every lane of the warp calls it, lanes without a walk pass valid = false.
+    // Lanes that must be waiting (query finished) before a warp of the persistent kernels runs a tail phase. The tail runs at the
+    // width of the waiting lanes, the traversal at the width of the rest: the costlier the tail (silhouette query + ray cast with a
+    // Neumann mesh, source lookups and triangle distances in 3D), the more lanes are worth waiting for. Round 1 found 6 for every
+    // variant; the oriented boxes made the queries ~3x shorter and moved the optimum (profiles/refill_sweep_r2.json: C3 2 373 M at 6,
+    // 2 455 M at 12; c1 1 388 M at 6, 1 759 M at 26, 1 546 M at 32; c4-small 409 / 577 / 487 M). WOST_REFILL_THRESHOLD overrides it (tuning).
+    inline int default_refill_threshold(int D, int F)
+    {
+        static const int env = []
+        {
+            const char *e = getenv("WOST_REFILL_THRESHOLD");
+            return e ? std::max(1, std::min(32, atoi(e))) : 0;
+        }();
+        if (env > 0)
+            return env;
+        return (D == 2 && F == 0) ? 12 : 24;
+    }
     // RefOrder: closest-point queries visit the tree in the reference's own order -- same results, kept as the
     // on-device stand-in for the reference's traversal cost (bench.py --walk-mode reforder).
     template <int D, bool RefOrder>
