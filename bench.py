@@ -143,8 +143,10 @@ def cpu_oracle_sample(wl, budget_s=12.0, nthreads=0, keep_field=False):
         t0 = time.perf_counter()
         sol, steps = orc.solve_uniform(prob, st, pixel_begin=r0 * W, pixel_end=(r0 + rows) * W, nthreads=cores)
         dt = time.perf_counter() - t0
-        if keep_field:  # the last (largest) chunk is kept for the parity check
-            first = (r0, r0 + rows, np.asarray(sol, np.float32).reshape(-1, 3)[r0 * W:(r0 + rows) * W].copy())
+        if keep_field:  # the chunk with the most evaluated pixels is kept for the parity check
+            npx = int(wl["mask"][r0:r0 + rows].sum()) if wl.get("mask") is not None else rows * W
+            if first is None or npx > first[3]:
+                first = (r0, r0 + rows, np.asarray(sol, np.float32).reshape(-1, 3)[r0 * W:(r0 + rows) * W].copy(), npx)
         total_steps += steps
         total_t += dt
         r0 += rows
@@ -287,10 +289,12 @@ class Bench:
         settings = api.make_settings((W, H), wl["depth"], wl["spp"], wl["eps"], seed=wl["seed"], spp_batch=spp_batch,
                                      walk_mode={"persistent": 1, "reforder": 2, "wavefront": 3, "persistent-reforder": 4}[walk_mode], **shard, **gkw)
 
-        def make_problem():
+        slices = wl.get("slices") or [{}]  # a slice set (c4-slices): one problem + integrator per evaluation plane, geometry shared
+
+        def make_problems():
             g_d = api.Scene(dim, wl["dverts"], wl["dprims"])
             g_n = api.Scene(dim, wl["nverts"], wl["nprims"]) if wl.get("nverts") is not None else None
-            return api.Problem(dim, dirichlet=g_d, neumann=g_n, **problem_kwargs(wl))
+            return [api.Problem(dim, dirichlet=g_d, neumann=g_n, **problem_kwargs(dict(wl, **ov))) for ov in slices]
 
         def make_integrator(p):
             it_ = api.GuidedIntegrator(p, settings, wl["network"]) if guided else api.UniformIntegrator(p, settings)
@@ -298,28 +302,49 @@ class Bench:
                 self.comm.attach(it_)  # ncclAllReduce of the gradient slab on the integrator's stream, per optimiser step (csrc/comm.cu)
             return it_
 
-        prob = make_problem()
-        it = make_integrator(prob)
+        class Group:
+            """the integrators of one step (one per slice), driven like a single one"""
+
+            def __init__(g):
+                g.probs = make_problems()
+                g.its = [make_integrator(p) for p in g.probs]
+
+            def solve(g):
+                g.device_ms, g.walk_steps, g.launches, g.kern_n, g.kern_ms = 0.0, 0, 0, 0, 0.0
+                for i in g.its:
+                    if guided:
+                        i.resetTraining()  # like elaina-exec: every solve starts from a freshly initialised network (exec.cu:104-123)
+                    i.solve()
+                    g.device_ms += i.last_device_ms
+                    g.walk_steps += i.last_walk_steps
+                    g.launches += i.launch_count
+                    n_, ms_ = i.step_kernel_time
+                    g.kern_n += n_
+                    g.kern_ms += ms_
+
+            def close(g):
+                for i in g.its:
+                    i.close()
+                for p_ in g.probs:
+                    p_.close()
+
+        grp = Group()
+        it = grp.its[0]
         for _ in range(warmup):
-            if guided:
-                it.resetTraining()
-            it.solve()
+            grp.solve()
         if sampler is not None and rank == 0:
             sampler.start()
         self.barrier()
         dev_ms, steps_total, launches, kern_ms, kern_launches = 0.0, 0, 0, 0.0, 0
         for _ in range(steps):
             self.flush.zero_()
-            if guided:
-                it.resetTraining()  # like elaina-exec: every solve starts from a freshly initialised network (exec.cu:104-123)
             torch.cuda.synchronize()
-            it.solve()
-            dev_ms += it.last_device_ms
-            steps_total += it.last_walk_steps
-            launches += it.launch_count
-            n, ms = it.step_kernel_time
-            kern_launches += n
-            kern_ms += ms
+            grp.solve()
+            dev_ms += grp.device_ms
+            steps_total += grp.walk_steps
+            launches += grp.launches
+            kern_launches += grp.kern_n
+            kern_ms += grp.kern_ms
         self.barrier()
         dev_ms = self.reduce(dev_ms, "max")
         kern_ms_max = self.reduce(kern_ms, "max")
@@ -329,7 +354,8 @@ class Bench:
         if world == 1 and rank == 0:
             relmse = relmse_analytic(wl, it.film())
         l2_window = it.l2_window_bytes
-        trav_full, trav_restricted = it.traversal_stats(reset=True)  # since creation: warm-up + timed solves
+        stats_ = [i.traversal_stats(reset=True) for i in grp.its]  # since creation: warm-up + timed solves
+        trav_full, trav_restricted = sum(x[0] for x in stats_), sum(x[1] for x in stats_)
         train_stats = dict(it.train_stats) if guided else None
         profile = it.profile if guided and os.environ.get("WOST_PROFILE") else None
 
@@ -339,26 +365,26 @@ class Bench:
             h2d += wl["nverts"].nbytes + wl["nprims"].nbytes + (wl["color_neumann"].nbytes if wl.get("color_neumann") is not None else 0)
         if wl.get("source") is not None:
             h2d += wl["source"].nbytes
-        d2h = W * H * 5 * 4
+        d2h = W * H * 5 * 4 * len(slices)
 
         def e2e_once():
             t_ = [time.perf_counter()]
-            p = make_problem()
+            g2 = Group()  # scenes (H2D + LBVH build), problems (H2D colours), integrators
             t_.append(time.perf_counter())
-            i2 = make_integrator(p)
+            g2.solve()
             t_.append(time.perf_counter())
-            i2.solve()
-            t_.append(time.perf_counter())
-            if self.comm is not None:
-                self.comm.gather_film(i2, 0, 0)  # final grid gather: owned row tiles -> rank 0 (packed rows over NVLink)
-            out = i2.film() if rank == 0 else None
+            out = None
+            for i2 in g2.its:
+                if self.comm is not None:
+                    self.comm.gather_film(i2, 0, 0)  # final grid gather: owned row tiles -> rank 0 (packed rows over NVLink)
+                if rank == 0:
+                    out = i2.film()
             t_.append(time.perf_counter())
             if os.environ.get("WOST_BENCH_DEBUG"):
-                print("e2e stages ms: problem %.1f integrator %.1f solve %.1f (device %.1f) gather+download %.1f" % (
-                    1e3 * (t_[1] - t_[0]), 1e3 * (t_[2] - t_[1]), 1e3 * (t_[3] - t_[2]), i2.last_device_ms, 1e3 * (t_[4] - t_[3])), file=sys.stderr, flush=True)
-            s = i2.last_walk_steps
-            i2.close()
-            p.close()
+                print("e2e stages ms: scenes+problems+integrators %.1f solve %.1f (device %.1f) gather+download %.1f" % (
+                    1e3 * (t_[1] - t_[0]), 1e3 * (t_[2] - t_[1]), g2.device_ms, 1e3 * (t_[3] - t_[2])), file=sys.stderr, flush=True)
+            s = g2.walk_steps
+            g2.close()
             return s, out
 
         n_e2e = max(1, min(steps, 3))
@@ -376,8 +402,7 @@ class Bench:
             e2e_value = self.reduce(float(e2e_steps), "sum") / e2e_t
             if rank == 0 and film is not None:
                 e2e_relmse = relmse_analytic(wl, film)  # N > 1: checks the gathered film
-        it.close()
-        prob.close()
+        grp.close()
         if rank != 0:
             return None
         peak, peak_src = measured_peak()
@@ -418,7 +443,7 @@ class Bench:
     def parity_check(self, wl, band):
         """the oracle's rows (cpu_baseline leg) against the GPU film of the same rows: same Philox streams, 1 spp -> bit-identical"""
         api = self.api
-        r0, r1, field = band
+        r0, r1, field = band[:3]
         W, H = wl["frame"]
         dim = wl["dim"]
         g_d = api.Scene(dim, wl["dverts"], wl["dprims"])

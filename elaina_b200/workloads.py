@@ -17,6 +17,7 @@ with the reference's keys, exec.cu:65-76 / core/problem.cu:158-181), runnable un
 elaina_b200/elaina-exec.
 """
 import json
+import math
 import os
 
 import numpy as np
@@ -94,6 +95,25 @@ def workload(name):
                     aabb_min=(-1.5, -1.5, -1.5), aabb_max=(1.5, 1.5, 1.5),
                     frame=(512, 512), depth=64, spp=64, eps=2e-3, seed=42, network=NETWORK_LADYBUG, bytes_per_step=1734,
                     desc="synthetic 3D Poisson, %d-triangle displaced icosphere, 512x512 slice z=0 masked to the interior (%d active pixels), 64 spp, depth 64" % (len(dp), int(mask.sum())))
+    if name in ("c4-slices", "c4-small-slices"):
+        # configs[3] as BASELINE.json words it: a SET of z-slices of the 512^3 evaluation volume. The bench runs `nslices` of the 512
+        # planes per step (evenly spaced over the part of the volume that cuts the mesh), each a 512^2 frame masked to the interior.
+        wl = workload("c4" if name == "c4-slices" else "c4-small")
+        nslices = 8
+        g = 2.0 * np.arange(512, dtype=np.float64) / 512 - 1.0
+        X, Y = np.meshgrid(g, g)
+        planes = (np.arange(nslices) + 0.5) / nslices * 2.0 - 1.0  # z in (-1, 1)
+        zs = 0.8 * planes
+        slices = []
+        for z in zs:
+            r = math.sqrt(max(0.0, 0.88 * 0.88 - z * z))
+            slices.append(dict(grid_pos=(0.0, 0.0, float(z)), mask=(np.hypot(X, Y) < r).astype(np.uint8)))
+        active = int(sum(int(sl["mask"].sum()) for sl in slices))
+        wl.update(name=name, slices=slices,
+                  desc=wl["desc"].replace("512x512 slice z=0 masked to the interior (%d active pixels)" % int(wl["mask"].sum()),
+                                          "%d of the 512 z-slices of the 512^3 evaluation volume per step (z = %s), each 512x512 masked to the interior (%d active pixels in total)"
+                                          % (nslices, ", ".join("%.2f" % z for z in zs), active)))
+        return wl
     if name.startswith("pin-"):
         return _pin_workload(name)
     raise SystemExit("unknown workload " + name)
