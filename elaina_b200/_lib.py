@@ -110,6 +110,7 @@ SYMBOLS = [
     ("wost_last_launch_count", c_int, [c_void_p, _PP(c_u64)]),
     ("wost_l2_window_bytes", c_int, [c_void_p, _PP(c_u64)]),
     ("wost_last_step_kernel_time", c_int, [c_void_p, _PP(c_u64), _PP(c_float)]),
+    ("wost_guided_last_samples", c_int, [c_void_p, c_void_p, c_u64, _PP(c_u64)]),
     ("wost_run_config", c_int, [c_char_p]),
     ("wost_comm_unique_id", c_int, [c_void_p]),
     ("wost_comm_create", c_int, [c_int, c_int, c_void_p, _PP(c_void_p)]),

@@ -456,6 +456,17 @@ class GuidedIntegrator(_Integrator):
         self._cb = _lib.ALLREDUCE_FN(tramp)
         check(_lib.load().wost_set_allreduce(self.h, ctypes.cast(self._cb, c_void_p), None))
 
+    def last_training_samples(self):
+        """the compacted training set of the last training frame -> dict(pos, dir, nrm, pdf, li, onN) like the oracle's emit_samples"""
+        n = c_u64()
+        L = _lib.load()
+        check(L.wost_guided_last_samples(self.h, None, 0, ctypes.byref(n)))
+        d = self.dim
+        rows = np.zeros((n.value, 3 * d + 3), np.float32)
+        if n.value:
+            check(L.wost_guided_last_samples(self.h, _p(rows), n.value, ctypes.byref(n)))
+        return dict(pos=rows[:, 0:d], dir=rows[:, d:2 * d], nrm=rows[:, 2 * d:3 * d], pdf=rows[:, 3 * d], li=rows[:, 3 * d + 1], onN=rows[:, 3 * d + 2] > 0.5)
+
     @property
     def profile(self):
         """device ms of the last solve by kernel class (needs WOST_PROFILE=1 in the environment)"""

@@ -10,7 +10,7 @@
 namespace wost
 {
     void set_last_error(const std::string &msg);
-    // Device allocations of libwost.so. Blocks >= 1 MiB are not returned to the driver when released but parked in a
+    // Device allocations of libwost.so. Blocks are not returned to the driver when released but parked in a
     // per-device free list keyed by exact size (scene.cu): re-creating a scene / problem / integrator of the same shape --
     // what a host does between solves -- then costs neither cudaMalloc nor cudaFree (the latter took up to 60 ms for the
     // accumulator and queue buffers). wost_trim_allocation_cache() hands everything back.

@@ -1869,6 +1869,37 @@ extern "C"
             ms8[k] = it->prof_ms[k];
         return WOST_OK;
     }
+    // parity probe: the compacted training set of the LAST training frame (generate_training_data, guided/train.h:422-471), one row
+    // per sample: pos[dim], dir[dim], nN[dim], dirPdf, Li, onN (3 * dim + 3 floats)
+    wost_status wost_guided_last_samples(wost_integrator *it, float *rows, uint64_t capacity_rows, uint64_t *n_rows)
+    {
+        if (!it || it->kind != WOST_GUIDED || !n_rows)
+            return WOST_ERR_INVALID;
+        const GuidedBuffers &g = it->gb;
+        const uint64_t n = std::min<uint64_t>(it->train_samples, (uint64_t)std::max(0, g.cap));
+        *n_rows = n;
+        if (!rows || n == 0)
+            return WOST_OK;
+        if (capacity_rows < n)
+        {
+            set_last_error("wost_guided_last_samples: buffer too small");
+            return WOST_ERR_INVALID;
+        }
+        const int D = it->dim, planes = 3 * D + 2, cap = g.cap;
+        std::vector<float> h((size_t)planes * cap);
+        std::vector<uint8_t> on((size_t)cap);
+        WOST_CUDA_TRY(cudaMemcpyAsync(h.data(), g.smp.ptr, sizeof(float) * h.size(), cudaMemcpyDeviceToHost, it->stream));
+        WOST_CUDA_TRY(cudaMemcpyAsync(on.data(), g.smp_onN.ptr, on.size(), cudaMemcpyDeviceToHost, it->stream));
+        WOST_CUDA_TRY(cudaStreamSynchronize(it->stream));
+        const int w = planes + 1;
+        for (uint64_t i = 0; i < n; ++i)
+        {
+            for (int k = 0; k < planes; ++k)
+                rows[i * w + k] = h[(size_t)k * cap + i];
+            rows[i * w + planes] = on[i] ? 1.0f : 0.0f;
+        }
+        return WOST_OK;
+    }
     wost_status wost_guided_last_stats(wost_integrator *it, uint64_t *train_samples, uint64_t *train_steps, float *last_loss)
     {
         if (!it)

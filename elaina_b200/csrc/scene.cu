@@ -39,7 +39,9 @@ namespace wost
             static AllocCache c;
             return c;
         }
-        constexpr size_t kCacheMinBytes = (size_t)1 << 20, kCacheMaxBytes = (size_t)16 << 30;
+        // every block is cached (a scene build makes ~50 small allocations; cudaMalloc + cudaFree of each cost more than the kernels
+        // that fill them): bounded by total bytes and by the number of parked blocks
+        constexpr size_t kCacheMinBytes = 1, kCacheMaxBytes = (size_t)16 << 30, kCacheMaxBlocks = 8192;
         bool alloc_cache_enabled()
         {
             static const bool on = getenv("WOST_NO_ALLOC_CACHE") == nullptr;
@@ -86,7 +88,7 @@ namespace wost
         {
             AllocCache &c = alloc_cache();
             std::lock_guard<std::mutex> lock(c.mu);
-            if (c.cached_bytes + bytes <= kCacheMaxBytes)
+            if (c.cached_bytes + bytes <= kCacheMaxBytes && c.free_blocks.size() < kCacheMaxBlocks)
             {
                 // The block is parked under the device that OWNS it, which need not be the current one (wost_set_device is
                 // public: one process may drive several GPUs and destroy a handle while another device is current).

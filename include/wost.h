@@ -277,6 +277,9 @@ extern "C"
      * [0] arrive (closest point + contributions), [1] bounce (MLP + sampling + move), [2] finish (uniform tail),
      * [3] gaps between classes, [4] training frames (samples + forward/backward + optimiser), [5..7] unused */
     wost_status wost_guided_last_profile(wost_integrator *it, float *ms8);
+    /* parity probe: the compacted training set of the last training frame (generate_training_data, integrator/guided/train.h:422-471),
+     * one row per sample: pos[dim], dir[dim], nN[dim], dirPdf, Li, onN -> 3 * dim + 3 floats. rows == NULL: only *n_rows. */
+    wost_status wost_guided_last_samples(wost_integrator *it, float *rows, uint64_t capacity_rows, uint64_t *n_rows);
     /* counters of the last guided solve: training samples consumed, optimiser steps, mean loss of the last batch */
     wost_status wost_guided_last_stats(wost_integrator *it, uint64_t *train_samples, uint64_t *train_steps, float *last_loss);
 

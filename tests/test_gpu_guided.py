@@ -309,6 +309,23 @@ def test_guided_training_samples_match_oracle(oracle):
     sol_o, _, smp = oracle.solve_guided(oprob, st, net, max_guided_depth=6, uniform_fraction=0.5, emit_samples=True)
     stats = it.train_stats
     assert abs(stats["samples"] - len(smp["li"])) <= 0.02 * len(smp["li"]) + 2
+    # the samples themselves (generate_training_data, train.h:422-471): same Philox draws and, with a fixed network, the same walks
+    # except where an fp16-level difference of a selection probability flips a decision -- every device sample must have a
+    # twin in the oracle's set (position, direction, normal, pdf, target, boundary flag), order aside
+    got = it.last_training_samples()
+    assert len(got["li"]) == stats["samples"]
+    key_o = np.concatenate([smp["pos"], smp["dir"]], 1).astype(np.float64)
+    key_g = np.concatenate([got["pos"], got["dir"]], 1).astype(np.float64)
+    d2 = ((key_g[:, None, :] - key_o[None, :, :]) ** 2).sum(-1)
+    j = d2.argmin(1)
+    twin = np.sqrt(d2[np.arange(len(j)), j]) < 1e-4
+    assert twin.mean() > 0.97, twin.mean()
+    jj = j[twin]
+    np.testing.assert_allclose(got["nrm"][twin], smp["nrm"][jj], atol=1e-5)
+    assert np.array_equal(got["onN"][twin], smp["onN"][jj] > 0)
+    # pdf and target depend on the network output (fp16 tensor-core forward vs the oracle's fp32 network): 2 % of the row's scale
+    assert np.mean(np.abs(got["pdf"][twin] - smp["pdf"][jj]) <= 0.02 * np.abs(smp["pdf"][jj]) + 1e-4) > 0.98
+    assert np.mean(np.abs(got["li"][twin] - smp["li"][jj]) <= 0.02 * np.abs(smp["li"][jj]) + 1e-3) > 0.95
     np.testing.assert_allclose(it.get_params(), params, atol=1e-7)  # lr = 0: weights untouched
     sol_g = it.film()[..., :3].reshape(-1, 3)
     assert np.isclose(sol_g, sol_o, rtol=2e-3, atol=2e-3).mean() > 0.9

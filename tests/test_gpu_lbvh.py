@@ -267,3 +267,52 @@ def test_oriented_boxes_contain_their_subtrees(name):
             # tight: the interval is the extent of the projections plus the widening (and fp32 rounding of the projection)
             slack = w + 4.0 * M * 2.0 ** -23
             assert np.all(pr.min(0) - lo <= 2.0 * slack) and np.all(hi - pr.max(0) <= 2.0 * slack), (name, i, side)
+
+
+def _degenerate_cases():
+    rng = np.random.RandomState(21)
+    cases = {}
+    # 2D: zero-length segments (both endpoints equal), duplicated segments, everything on one line, coordinates of very different scale
+    pts = rng.rand(400, 2).astype(np.float32)
+    idx = rng.randint(0, 400, (900, 2)).astype(np.int32)
+    idx[:60, 1] = idx[:60, 0]                      # zero-length
+    idx[60:120] = idx[120:180]                     # duplicates
+    cases["degenerate2d"] = (2, pts, idx)
+    line = np.stack([np.linspace(-3, 3, 300), np.full(300, 0.25)], 1).astype(np.float32)
+    cases["collinear2d"] = (2, line, np.stack([np.arange(299), np.arange(1, 300)], 1).astype(np.int32))
+    big = (rng.rand(500, 2) * np.array([1e5, 1e-2])).astype(np.float32)
+    bidx = rng.randint(0, 500, (800, 2)).astype(np.int32)
+    cases["anisotropic2d"] = (2, big, bidx[bidx[:, 0] != bidx[:, 1]])
+    # 3D: needle and sliver triangles, a flat (coplanar) sheet, duplicated triangles
+    v = rng.rand(600, 3).astype(np.float32)
+    v[:200, 2] = 0.5                               # coplanar sheet
+    t = rng.randint(0, 200, (500, 3)).astype(np.int32)
+    t = t[(t[:, 0] != t[:, 1]) & (t[:, 1] != t[:, 2]) & (t[:, 0] != t[:, 2])]
+    needle = np.stack([np.arange(200, 590), np.arange(201, 591), np.arange(202, 592)], 1).astype(np.int32)
+    v[200:] = np.cumsum(rng.randn(400, 3).astype(np.float32) * np.array([1e-1, 1e-5, 1e-5], np.float32), 0)  # nearly collinear chain -> slivers
+    cases["slivers3d"] = (3, v, np.concatenate([t, needle, t[:50]], 0))
+    return cases
+
+
+@pytest.mark.parametrize("name", ["degenerate2d", "collinear2d", "anisotropic2d", "slivers3d"])
+def test_degenerate_meshes_match_oracle(oracle, name):
+    """Edge cases of the oriented-box records (zero normals, zero-length axes, flat and needle-shaped subtrees, duplicated
+    primitives = exact ties everywhere): closest-point and silhouette results stay bit-identical to the oracle, and every
+    vertex stays inside the oriented boxes of its ancestors (the build never produces a NaN frame)."""
+    api = _api()
+    dim, v, p = _degenerate_cases()[name]
+    so, sg = oracle.scene(dim, v, p), api.Scene(dim, v, p)
+    rec, _ = sg.dump_traversal_layout()
+    assert np.isfinite(rec[:, (10 if dim == 2 else 16):(22 if dim == 2 else 40)]).all()
+    q, d, md, u, rad = random_queries(v, 20000, 6, margin=0.5)
+    io, do = so.nearest(q)
+    ig, dg = sg.nearest(q)
+    assert np.array_equal(bits(do), bits(dg))
+    assert np.array_equal(io, ig)
+    for flip in (False, True):
+        assert np.array_equal(bits(so.silhouette(q, flip)), bits(sg.silhouette(q, flip)))
+    # on the primitives themselves (distance 0, many exact ties)
+    on = v[p[:, 0]][:3000]
+    io, do = so.nearest(on)
+    ig, dg = sg.nearest(on)
+    assert np.array_equal(bits(do), bits(dg)) and np.array_equal(io, ig)
