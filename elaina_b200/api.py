@@ -293,12 +293,15 @@ class _Integrator:
     def renderSource(self):
         check(_lib.load().wost_render_channel(self.h, CH_SOURCE))
 
-    def film(self, channel=CH_SOLUTION):
-        """(H, W, 5) float32: r, g, b, a, weight -- util/film.h layout, index x + y*W, not flipped."""
+    def film(self, channel=CH_SOLUTION, out=None):
+        """(H, W, 5) float32: r, g, b, a, weight -- util/film.h layout, index x + y*W, not flipped.
+        out: optional preallocated C-contiguous float32 array of that shape (e.g. a view of pinned host memory) to download into."""
         w, h = self.settings.frame_w, self.settings.frame_h
-        out = np.zeros((h, w, 5), np.float32)
+        if out is None:
+            out = np.empty((h, w, 5), np.float32)
+        assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"] and out.size == h * w * 5
         check(_lib.load().wost_film_download(self.h, channel, _p(out)))
-        return out
+        return out.reshape(h, w, 5)
 
     def film_stderr(self):
         """(H, W, 3) measured standard error of the solution of the last solve (wost_film_stderr); exact per-pixel sample

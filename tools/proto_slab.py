@@ -179,12 +179,66 @@ def main():
             if cur < 0:
                 return best, win, opens, evals
 
+    def query_deferred(q, bound, K):
+        """nearest-first traversal with OBB pruning where leaf distances are evaluated only every K trips (warp-level leaf rounds)
+        or when the lane has nothing else to do; returns (best, opens, evals, idle_trips)"""
+        best = bound
+        opens = evals = idle = 0
+        st = []
+        cur = 0
+        pend = []
+        trip = 0
+        while True:
+            trip += 1
+            if trip % K == 0 and pend:
+                for pos in pend:
+                    evals += 1
+                    d = prim_d(pos, q)
+                    if d <= best:
+                        best = d
+                pend = []
+            if cur < 0:
+                # pop
+                while st:
+                    d2, ch = st.pop()
+                    if d2 <= best * best:
+                        cur = ch
+                        break
+                if cur < 0:
+                    if pend:
+                        idle += 1   # drained: wait for the next leaf round
+                        continue
+                    return best, opens, evals, idle
+            opens += 1
+            kids = []
+            for ch in (left[cur], right[cur]):
+                d2 = max(box_d2(ch, q), slab_d2(ch, q))
+                kids.append((d2, ch))
+            kids.sort()
+            nxt = []
+            for d2, ch in kids:
+                if d2 > best * best:
+                    continue
+                if is_leaf[ch]:
+                    pend.append(ch - (N - 1))
+                else:
+                    nxt.append((d2, ch))
+            if len(nxt) == 2:
+                st.append(nxt[1])
+                cur = nxt[0][1]
+            elif len(nxt) == 1:
+                cur = nxt[0][1]
+            else:
+                cur = -1
+
     rng = np.random.RandomState(5)
     W, H = wl["frame"]
     mask = wl.get("mask")
     pix = np.flatnonzero(mask.reshape(-1)) if mask is not None else np.arange(W * H)
     eps = wl["eps"]
     tot = {False: [0, 0], True: [0, 0]}
+    DEFER = [1, 2, 3, 4, 6] if os.environ.get('OBB') == '1' else []
+    dstat = {}
     nq = 0
     hist = []
     for w in range(nwalks):
@@ -213,11 +267,18 @@ def main():
                 else:
                     assert abs(r - r0[0]) < 1e-9, (r, r0)
                     hist.append((r0[0], r0[2], r0[3], o, e))
+            for K in DEFER:
+                rb, o_, e_, i_ = query_deferred(x, bound, K)
+                assert abs(rb - r0[0]) < 1e-9
+                dstat.setdefault(K, [0, 0, 0])
+                dstat[K][0] += o_; dstat[K][1] += e_; dstat[K][2] += i_
             R, win = r0[0], r0[1]
             nq += 1
     print("%s: %d queries" % (name, nq))
     for k in (False, True):
         print("  slab=%s: node opens/query %.1f, leaf evals/query %.1f" % (k, tot[k][0] / nq, tot[k][1] / nq))
+    for K, v in dstat.items():
+        print('  deferred leaves, round every %d trips: opens/query %.1f evals/query %.1f idle trips/query %.2f' % (K, v[0] / nq, v[1] / nq, v[2] / nq))
     h = np.array(hist)
     qs = np.quantile(h[:, 0], [0.25, 0.5, 0.75])
     for a, b in ((0, qs[0]), (qs[0], qs[1]), (qs[1], qs[2]), (qs[2], 1e30)):
