@@ -171,6 +171,7 @@ namespace wost
         float4 *acc; // [slot][active rank]
         int max_depth;
         int refill_threshold;
+        int stack_levels; // shared-memory levels of the traversal stack (deeper levels spill to local memory)
         int *cursor;
         unsigned long long *steps;
         int *overflow;
@@ -188,7 +189,7 @@ namespace wost
         extern __shared__ uint2 smem_stack[];
         SmemStack st;
         uint2 spill_mem[kSpillLevels];
-        st.init(smem_stack, a.overflow, spill_mem);
+        st.init(smem_stack, a.overflow, spill_mem, a.stack_levels);
         const int lane = threadIdx.x & 31;
         const long long njobs = (long long)a.n_active * a.batch_samples;
         WalkState<D> w;
@@ -602,7 +603,9 @@ namespace wost
         const int S = it->spp_batch;
         const int spp = it->s.samples_per_pixel;
         cudaStream_t st = it->stream;
-        const size_t smem = stack_smem_bytes(kWalkBlock);
+        const size_t smem_first = stack_smem_bytes(kWalkBlock);
+        const int stack_levels = walk_stack_levels(D, F);
+        const size_t smem = stack_smem_bytes(kWalkBlock, stack_levels);
         int occ = 1;
         WOST_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_walk_persistent<D, RefOrder, F>, kWalkBlock, smem));
         const int grid_full = sm_count() * std::max(1, occ);
@@ -639,7 +642,7 @@ namespace wost
                 return WOST_ERR_CUDA;
             }
             const int grid = std::max(1, std::min(grid_full, div_up(it->n_active, kWalkBlock)));
-            k_first_hit<D, RefOrder><<<grid, kWalkBlock, smem, st>>>(ctx, it->d_active.ptr, it->n_active, it->d_first.ptr, it->d_overflow.ptr);
+            k_first_hit<D, RefOrder><<<grid, kWalkBlock, smem_first, st>>>(ctx, it->d_active.ptr, it->n_active, it->d_first.ptr, it->d_overflow.ptr);
             ++it->launches;
         }
         for (int bi = 0; bi < nbatches; ++bi)
@@ -656,6 +659,7 @@ namespace wost
             a.acc = it->d_acc.ptr;
             a.max_depth = it->s.max_walking_depth;
             a.refill_threshold = refill_threshold;
+            a.stack_levels = stack_levels;
             a.cursor = it->d_counts.ptr;
             a.steps = it->d_steps.ptr;
             a.overflow = it->d_overflow.ptr;

@@ -560,6 +560,20 @@ namespace wost
             return env;
         return (D == 2 && F == 0) ? 12 : 24;
     }
+    // Shared-memory levels of the traversal stack in the persistent walk kernels (deeper levels spill to thread-local memory). The
+    // stacks of 9 resident CTAs x 20 levels take 180 KB of the SM's 256 KB and leave ~50 KB of L1 for the node records; with the
+    // oriented boxes few far siblings are ever pending, so a shorter shared stack trades rare spills for L1 hits on the top levels.
+    // WOST_STACK_LEVELS overrides it (tuning).
+    inline int walk_stack_levels(int D, int F)
+    {
+        static const int env = []
+        {
+            const char *e = getenv("WOST_STACK_LEVELS");
+            return e ? std::max(1, std::min(kSmemLevels, atoi(e))) : 0;
+        }();
+        (void)F;
+        return env > 0 ? env : (D == 2 ? 12 : kSmemLevels); // sweep (profiles/stack_levels_r2.json): 2D 12 (+1-2 %), 3D the full 20
+    }
     // RefOrder: closest-point queries visit the tree in the reference's own order -- same results, kept as the
     // on-device stand-in for the reference's traversal cost (bench.py --walk-mode reforder).
     template <int D, bool RefOrder>
