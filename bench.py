@@ -426,7 +426,7 @@ class Bench:
         rec = {"value": value, "unit": UNIT, "ms_per_step": dev_ms / steps, "steps": steps, "warmup": warmup,
                "config": {"workload": wl["desc"], "integrator": integrator,
                           "walk_mode": walk_mode if not guided else ("fused tcgen05 bounce kernel" if mlp_impl == 0 else "validation: SIMT MLP through HBM"),
-                          "relmse_vs_analytic": relmse, "spp_batch": spp_batch or "auto (~16M walks in flight)",
+                          "relmse_vs_analytic": relmse, "spp_batch": spp_batch or "auto (~64M walks in flight uniform, ~16M guided)",
                           "walk_steps_per_step": steps_all / steps, "sharding": "interleaved 4-row tiles over %d ranks" % world,
                           "l2": "256 MiB flush between timed steps", "l2_window_bytes": int(l2_window),
                           "closest_point_second_passes_per_walk_step": trav_restricted / max(1.0, float(steps_total) * (steps + warmup) / steps),

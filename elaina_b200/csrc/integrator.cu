@@ -850,8 +850,11 @@ extern "C"
         int S = s.spp_batch;
         if (S <= 0)
         {
-            // auto: keep ~16M walks in flight (queues 2 x 32..36 B/item + 16 B/slot-pixel accumulators)
-            const long long target = 16ll << 20;
+            // auto: walks in flight per launch. Persistent uniform kernel: ~64M (16 B of accumulator per walk; fewer launches = fewer
+            // drain phases: C3 2 454 M at 44 spp per launch, 2 505 M at 256). Wavefront modes and the guided integrator also hold
+            // 64-100 B of queue per walk: ~16M.
+            const bool persistent_uniform = kind == WOST_UNIFORM && s.walk_mode != WOST_MODE_REFERENCE_ORDER && s.walk_mode != WOST_MODE_WAVEFRONT;
+            const long long target = persistent_uniform ? (64ll << 20) : (16ll << 20);
             S = (int)std::max<long long>(1, target / std::max(1, it->n_active));
         }
         S = std::max(1, std::min(S, s.samples_per_pixel));
@@ -867,7 +870,8 @@ extern "C"
         };
         if (it->d_active.upload(active.data(), active.size()) != cudaSuccess)
             return fail("active pixel upload");
-        for (int i = 0; i < 2 && kind == WOST_UNIFORM; ++i)
+        // ping-pong queues: wavefront modes only (the persistent kernel keeps its walks in registers)
+        for (int i = 0; i < 2 && kind == WOST_UNIFORM && (s.walk_mode == WOST_MODE_REFERENCE_ORDER || s.walk_mode == WOST_MODE_WAVEFRONT); ++i)
         {
             if (it->qa[i].alloc(it->queue_capacity) != cudaSuccess || it->qb[i].alloc(it->queue_capacity) != cudaSuccess)
                 return fail("queue allocation");
