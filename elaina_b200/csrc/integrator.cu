@@ -831,20 +831,24 @@ extern "C"
         const uint8_t *mask = problem->desc.mask;
         // frame-wide count of evaluated pixels: identical on every rank whatever its pixel range / shard (it sizes the
         // data-parallel training batches, so that all ranks issue the same number of gradient all-reduces)
-        for (int p = 0; p < it->npix; ++p)
-            if (!mask || mask[p])
-                ++it->n_active_frame;
-        for (int p = pb; p < pe; ++p)
+        if (mask)
         {
-            if (mask && !mask[p])
-                continue;
-            if (s.pixel_stride_rows > 0 && s.num_shards > 1)
-            {
-                const int row = p / s.frame_w;
-                if ((row / s.pixel_stride_rows) % s.num_shards != s.shard)
-                    continue;
-            }
-            active.push_back((uint32_t)p);
+            int cnt = 0;
+            for (int p = 0; p < it->npix; ++p) // branch-free: vectorised by the compiler
+                cnt += mask[p] != 0;
+            it->n_active_frame = cnt;
+        }
+        else
+            it->n_active_frame = it->npix;
+        const bool sharded = s.pixel_stride_rows > 0 && s.num_shards > 1;
+        for (int row = pb / s.frame_w; row <= (pe - 1) / s.frame_w && pe > pb; ++row)
+        {
+            if (sharded && (row / s.pixel_stride_rows) % s.num_shards != s.shard)
+                continue; // rows of other shards are skipped whole
+            const int p0 = std::max(pb, row * s.frame_w), p1 = std::min(pe, (row + 1) * s.frame_w);
+            for (int p = p0; p < p1; ++p)
+                if (!mask || mask[p])
+                    active.push_back((uint32_t)p);
         }
         it->n_active = (int)active.size();
         int S = s.spp_batch;
