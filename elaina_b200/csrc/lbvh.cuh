@@ -726,13 +726,16 @@ namespace wost
             const NodeViewE<D> n = load_tnode_e(rec);
             float Le = box_mindist(n.le, q), Re = box_mindist(n.re, q);
             bool goL = Le <= t.thr, goR = Re <= t.thr;
-            // children that pass on their AABB are tested against their oriented box as well (pruning only, see Obb)
-            if (goL)
+            // children that pass on their AABB are tested against their oriented box as well (pruning only, see Obb). Not in the
+            // distance-only far-field phases (>= 3): their slack is 2^-21 |q|, below the rounding of a projection onto the frame
+            // (~2^-20 |q|), and that far from the mesh every box looks like a point anyway.
+            const bool use_obb = D == 3 || t.phase < 3;
+            if (goL && use_obb)
             {
                 Le = fmax_nn(Le, obb_mindist2(load_obb(rec, 0), q));
                 goL = Le <= t.thr;
             }
-            if (goR)
+            if (goR && use_obb)
             {
                 Re = fmax_nn(Re, obb_mindist2(load_obb(rec, 1), q));
                 goR = Re <= t.thr;

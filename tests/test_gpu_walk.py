@@ -197,3 +197,24 @@ def test_reference_order_mode_is_identical(oracle):
     for f, steps in films[1:]:
         assert steps == films[0][1]
         assert np.array_equal(bits(f), bits(films[0][0]))
+
+
+@pytest.mark.parametrize("name,frame,spp", [("c1", 96, 2), ("c2", 128, 2)])
+def test_real_geometry_walks_bit_exact(oracle, name, frame, spp):
+    """BASELINE configs[0] / configs[1] on their real geometry (data/ladybug: 61 476 segments, data/fille: 66 367 segments, depth 128,
+    both inside the shipped Neumann square): the whole walker -- 64-bit Morton tree, oriented-box pruning, silhouette query, ray
+    casts, far-field phases for the walks that leak through the corners of the Neumann square (fille) -- against the oracle,
+    film and walk-step count bit for bit."""
+    from elaina_b200 import api
+    from elaina_b200.workloads import workload, problem_kwargs
+    wl = workload(name)
+    dim = wl["dim"]
+    kw = problem_kwargs(wl)
+    oprob = dict(dim=dim, dirichlet=oracle.scene(dim, wl["dverts"], wl["dprims"]), neumann=oracle.scene(dim, wl["nverts"], wl["nprims"]), **kw)
+    gprob = api.Problem(dim, dirichlet=api.Scene(dim, wl["dverts"], wl["dprims"]), neumann=api.Scene(dim, wl["nverts"], wl["nprims"]), **kw)
+    st = _settings(frame, frame, wl["depth"], spp, wl["eps"], 5)
+    sol_o, steps_o = oracle.solve_uniform(oprob, st, nthreads=0)
+    it = api.UniformIntegrator(gprob, api.make_settings((frame, frame), wl["depth"], spp, wl["eps"], seed=5, spp_batch=1))
+    it.solve()
+    assert it.last_walk_steps == steps_o
+    assert np.array_equal(bits(it.film()[..., :3].reshape(-1, 3)), bits(sol_o))
