@@ -218,3 +218,28 @@ def test_real_geometry_walks_bit_exact(oracle, name, frame, spp):
     it.solve()
     assert it.last_walk_steps == steps_o
     assert np.array_equal(bits(it.film()[..., :3].reshape(-1, 3)), bits(sol_o))
+
+
+def test_uniform_3d_tessellated_poisson_bit_exact(oracle):
+    """C4's shape at a size the oracle finishes in seconds: 81 920-triangle displaced icosphere (shared edges and vertices
+    everywhere = exact ties -> restricted second passes), Poisson source grid, slice through the centre. Film, walk-step count and
+    the second-pass machinery against the oracle, bit for bit."""
+    from elaina_b200 import api, scenes
+    dv, dp = scenes.icosphere(6, 1.0, 0.1)
+    W = 56
+    g = 2.0 * np.arange(W, dtype=np.float64) / W - 1.0
+    X, Y = np.meshgrid(g, g)
+    spec = dict(dim=3, dverts=dv, dprims=dp, color_dirichlet=scenes.gray_pairs(scenes.harmonic_3d(dv)),
+                source=np.ones((16, 16, 16, 3), np.float32), source_origin=(-1.6, -1.6, -1.6), source_voxel=0.2,
+                mask=(np.hypot(X, Y) < 0.88).astype(np.uint8),
+                grid_scale=1.0, grid_pos=(0.0, 0.0, 0.0), grid_up=(0.0, 1.0, 0.0), grid_right=(1.0, 0.0, 0.0),
+                aabb_min=(-1.5, -1.5, -1.5), aabb_max=(1.5, 1.5, 1.5))
+    oprob, gprob = build_both(oracle, spec)
+    st = _settings(W, W, 64, 2, 2e-3, 42)
+    sol_o, steps_o = oracle.solve_uniform(oprob, st, nthreads=0)
+    it = api.UniformIntegrator(gprob, api.make_settings((W, W), 64, 2, 2e-3, seed=42, spp_batch=1))
+    it.solve()
+    assert it.last_walk_steps == steps_o
+    assert np.array_equal(bits(it.film()[..., :3].reshape(-1, 3)), bits(sol_o))
+    full, restricted = it.traversal_stats()
+    assert restricted > 0 and full == 0   # ties were met and resolved by the restricted pass, never by a full reference-order traversal
