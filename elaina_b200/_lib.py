@@ -88,6 +88,7 @@ SYMBOLS = [
     ("wost_scene_dump_sorted", c_int, [c_void_p, c_void_p, c_void_p]),
     ("wost_scene_dump_traversal_layout", c_int, [c_void_p, c_void_p, _PP(c_int), c_void_p]),
     ("wost_lbvh_nearest", c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    ("wost_lbvh_nearest_static", c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     ("wost_lbvh_silhouette", c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
     ("wost_lbvh_ray", c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     ("wost_lbvh_ray_any", c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

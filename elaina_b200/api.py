@@ -110,6 +110,15 @@ class Scene:
         check(_lib.load().wost_lbvh_nearest(self.h, _p(pts), len(pts), _p(idx), _p(dist)))
         return idx, dist
 
+    def nearest_static(self, pts):
+        """wost_lbvh_nearest_static: same answer as nearest(), staged through the library's fixed device array (no allocation;
+        at most MAX_STATIC_POINTS points per call, one call at a time per GPU)."""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, self.dim)
+        idx = np.zeros(len(pts), np.uint32)
+        dist = np.zeros(len(pts), np.float32)
+        check(_lib.load().wost_lbvh_nearest_static(self.h, _p(pts), len(pts), _p(idx), _p(dist)))
+        return idx, dist
+
     def silhouette(self, pts, flip=False):
         pts = np.ascontiguousarray(pts, np.float32).reshape(-1, self.dim)
         dist = np.zeros(len(pts), np.float32)

@@ -1492,6 +1492,42 @@ namespace wost
         }
         return WOST_OK;
     }
+    // ------------------------------------------------------------------ closest-point queries without any allocation
+    // Staging area of wost_lbvh_nearest_static(): a fixed array in the library's device image, so the entry point never asks
+    // the driver (or libwost's own block cache) for memory. Every GPU that loads libwost.so carries these ~1.25 MiB until the
+    // process exits. Layout in 32-bit words:
+    //   [0, 64)                         control words of the traversal (SmemStack::overflow: [0] stack-overflow flag,
+    //                                   [1], [2] traversal statistics, [8, 24) debug counters) -- zeroed at the start of each call
+    //   [64, 64 + 3 M)                  query points (n * dim floats)
+    //   [64 + 3 M, 64 + 4 M)            closest primitive per query
+    //   [64 + 4 M, 64 + 5 M)            distance per query                       with M = kStaticNearestMaxPoints
+    constexpr int kStaticNearestMaxPoints = WOST_NEAREST_STATIC_MAX_POINTS;
+    constexpr int kStaticCtrlWords = 64;
+    constexpr size_t kStaticScratchWords = kStaticCtrlWords + (size_t)5 * kStaticNearestMaxPoints;
+    static __device__ __align__(256) uint32_t g_nearest_static_scratch[kStaticScratchWords];
+
+    // In host code `g_nearest_static_scratch` is only a handle for the runtime, not somewhere a kernel can read or write: the
+    // device address has to be asked for, per device, while that device is current. It is looked up once per GPU and kept.
+    constexpr int kStaticMaxDevices = 64;
+    static std::mutex g_static_scratch_mu;
+    static uint32_t *g_static_scratch_addr[kStaticMaxDevices] = {};
+    static wost_status static_scratch_for_current_device(int device, uint32_t **out)
+    {
+        std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+        if (!g_static_scratch_addr[device])
+        {
+            uint32_t *p = nullptr;
+            WOST_CUDA_TRY(cudaGetSymbolAddress((void **)&p, g_nearest_static_scratch));
+            if (!p)
+            {
+                set_last_error("wost_lbvh_nearest_static: cudaGetSymbolAddress returned a null scratch address");
+                return WOST_ERR_CUDA;
+            }
+            g_static_scratch_addr[device] = p;
+        }
+        *out = g_static_scratch_addr[device];
+        return WOST_OK;
+    }
 } // namespace wost
 
 using namespace wost;
@@ -1803,6 +1839,65 @@ extern "C"
         WOST_CUDA_TRY(d_obj.download(obj, n));
         WOST_CUDA_TRY(d_pdf.download(pdf, n));
         WOST_CUDA_TRY(cudaDeviceSynchronize());
+        return WOST_OK;
+    }
+
+    // ---- host-buffer closest-point query that allocates nothing (include/wost.h has the contract)
+    wost_status wost_lbvh_nearest_static(const wost_scene *s, const float *pts, int n, uint32_t *idx, float *dist)
+    {
+        if (!s || !pts || !dist || n < 0)
+        {
+            set_last_error("wost_lbvh_nearest_static: invalid argument");
+            return WOST_ERR_INVALID;
+        }
+        if (n > kStaticNearestMaxPoints)
+        {
+            char buf[192];
+            snprintf(buf, sizeof(buf), "wost_lbvh_nearest_static: %d query points exceed the fixed scratch of %d points; split the batch or call wost_lbvh_nearest",
+                     n, kStaticNearestMaxPoints);
+            set_last_error(buf);
+            return WOST_ERR_INVALID;
+        }
+        if (n == 0)
+            return WOST_OK;
+        int cur = -1;
+        WOST_CUDA_TRY(cudaGetDevice(&cur));
+        if (cur != s->device || cur < 0 || cur >= kStaticMaxDevices)
+        {
+            char buf[192];
+            snprintf(buf, sizeof(buf), "wost_lbvh_nearest_static: the scene lives on device %d but device %d is current (wost_set_device first; devices 0..%d)",
+                     s->device, cur, kStaticMaxDevices - 1);
+            set_last_error(buf);
+            return WOST_ERR_INVALID;
+        }
+        uint32_t *scratch = nullptr;
+        wost_status rc = static_scratch_for_current_device(cur, &scratch);
+        if (rc != WOST_OK)
+            return rc;
+        int *d_ctrl = reinterpret_cast<int *>(scratch);
+        float *d_pts = reinterpret_cast<float *>(scratch + kStaticCtrlWords);
+        uint32_t *d_idx = scratch + kStaticCtrlWords + (size_t)3 * kStaticNearestMaxPoints;
+        float *d_dist = reinterpret_cast<float *>(scratch + kStaticCtrlWords + (size_t)4 * kStaticNearestMaxPoints);
+        // the array still holds whatever the previous call left: the overflow flag and the counters must start at zero
+        WOST_CUDA_TRY(cudaMemsetAsync(d_ctrl, 0, kStaticCtrlWords * sizeof(uint32_t), nullptr));
+        WOST_CUDA_TRY(cudaMemcpyAsync(d_pts, pts, (size_t)n * s->dim * sizeof(float), cudaMemcpyHostToDevice, nullptr));
+        const size_t sm = stack_smem_bytes(kQueryBlock);
+        if (s->dim == 2)
+            k_nearest<2><<<query_grid(n), kQueryBlock, sm>>>(s->view<2>(), d_pts, n, d_idx, d_dist, d_ctrl);
+        else
+            k_nearest<3><<<query_grid(n), kQueryBlock, sm>>>(s->view<3>(), d_pts, n, d_idx, d_dist, d_ctrl);
+        WOST_CUDA_TRY(cudaGetLastError());
+        int overflowed = 0;
+        WOST_CUDA_TRY(cudaMemcpyAsync(dist, d_dist, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, nullptr));
+        if (idx)
+            WOST_CUDA_TRY(cudaMemcpyAsync(idx, d_idx, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, nullptr));
+        WOST_CUDA_TRY(cudaMemcpyAsync(&overflowed, d_ctrl, sizeof(int), cudaMemcpyDeviceToHost, nullptr));
+        WOST_CUDA_TRY(cudaStreamSynchronize(nullptr));
+        if (overflowed)
+        {
+            set_last_error("LBVH traversal stack overflow (tree deeper than 64 levels)");
+            return WOST_ERR_OVERFLOW;
+        }
         return WOST_OK;
     }
 }

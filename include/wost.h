@@ -72,6 +72,31 @@ extern "C"
     /* lbvh::sample_object_in_sphere -- core/sample.cuh:23-92. obj = -1 when nothing was selected. */
     wost_status wost_lbvh_sample_sphere(const wost_scene *scene, const float *ctr, const float *radius, const float *u, int n,
                                         int *obj, float *pdf);
+    /* Closest-point query for hosts that must not allocate GPU memory. No counterpart in the reference (Elaina allocates
+     * freely and never frees, integrator/uniform/integrator.cu:25-60); it exists for the embedders of this library that
+     * cannot afford wost_lbvh_nearest's three staging buffers per call:
+     *   - applications that hand the whole card to their own pool at start-up (renderers, DCC plug-ins, inference
+     *     servers), where a later cudaMalloc from a plug-in fails or eats into a budget someone else planned;
+     *   - frame loops and other latency-bound threads: cudaMalloc / cudaFree serialise against all work on the device, so
+     *     one call stalls every stream of the process;
+     *   - code running after set-up in a sandbox whose policy is "no allocation after initialisation".
+     * Same arguments, same results and same error codes as wost_lbvh_nearest (host buffers in, host buffers out, idx may
+     * be NULL), but the points and results are staged through a fixed array compiled into libwost.so instead of freshly
+     * allocated blocks. Consequences of that design:
+     *   - n is limited to WOST_NEAREST_STATIC_MAX_POINTS per call; a larger n is refused with WOST_ERR_INVALID and a
+     *     message naming the limit (split the batch, or use wost_lbvh_nearest). The array costs about 1.25 MiB of device
+     *     memory on every GPU the process loads the library on, for the lifetime of the process;
+     *   - the scene's device must be the current one (wost_set_device); otherwise WOST_ERR_INVALID;
+     *   - the first call on each device also looks up the array's device address (cudaGetSymbolAddress) and makes the
+     *     CUDA runtime load the kernel; make that first call during set-up, before any stream capture begins;
+     *   - the call itself invokes no cudaMalloc, cudaFree or allocating library routine. It runs on the default stream and
+     *     returns after the results are in `idx` / `dist`;
+     *   - all calls on one device share the one array, which keeps the previous call's contents (the control words are
+     *     zeroed at the start of each call). Two calls in flight on the same GPU at once (two host threads, whether on
+     *     one scene or on different scenes) would overwrite each other's points and results: serialise them;
+     *   - its traversals are not added to wost_scene_traversal_stats (those counters live in the scene's own block). */
+#define WOST_NEAREST_STATIC_MAX_POINTS 65536
+    wost_status wost_lbvh_nearest_static(const wost_scene *scene, const float *pts, int n, uint32_t *idx, float *dist);
     /* Device-resident variants used by bench.py (all pointers are device pointers on the scene's GPU;
      * launched on `stream`, a cudaStream_t passed as void*; no synchronisation). */
     wost_status wost_lbvh_nearest_dev(const wost_scene *scene, const float *d_pts, int n, uint32_t *d_idx, float *d_dist, void *stream);
