@@ -351,6 +351,7 @@ namespace wost
     }
 
     constexpr int kBounceStackLevels = 12;
+    static_assert(kBounceStackLevels >= kMinSmemLevels && kBounceStackLevels <= kSmemLevels, "spill area is sized for kMinSmemLevels");
     // ---- one guided bounce
     template <int D, int K0>
     __global__ void __launch_bounds__(kGBlock) k_g_bounce(const __grid_constant__ WalkCtx<D> c, const __grid_constant__ GArgs a, const __grid_constant__ GuideNetView net)

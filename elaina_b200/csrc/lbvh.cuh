@@ -313,8 +313,12 @@ namespace wost
     // Shared-memory stack, one column per thread: entry(level, tid) = base[level * blockDim + tid].
     // Consecutive lanes hit consecutive 8-byte slots -> conflict-free. The first kSmemLevels levels live in shared memory, deeper ones
     // (real scenes need <= 26 in total) spill to local memory; beyond 64 (the reference's limit) a flag is raised.
-    constexpr int kSmemLevels = 20; // short stack in shared memory (20 KB per 128-thread CTA: 11 CTAs per SM)
-    constexpr int kSpillLevels = 44; // deeper levels spill to local memory (reference limit: 64 in total)
+    // The TOTAL is 64 entries whatever share of it a kernel keeps in shared memory (20, or 12 in the 2D walker and the bounce
+    // kernel): the spill area is sized for the smallest share any kernel may ask for.
+    constexpr int kStackCapacity = 64; // the reference's stack[64] (core/query.cuh:250)
+    constexpr int kSmemLevels = 20;    // short stack in shared memory (20 KB per 128-thread CTA: 11 CTAs per SM)
+    constexpr int kMinSmemLevels = 8;  // fewest shared-memory levels a kernel may configure (WOST_STACK_LEVELS is clamped to it)
+    constexpr int kSpillLevels = kStackCapacity - kMinSmemLevels; // thread-local entries behind the shared-memory levels
     struct StackEntry
     {
         uint32_t ref;
@@ -331,10 +335,10 @@ namespace wost
         int levels; // entries of this stack that live in shared memory (kSmemLevels unless the kernel asked for fewer)
         int *overflow; // [0] stack overflow flag, [1] full reference-order traversals, [2] restricted second passes (statistics)
         uint2 *spill; // kSpillLevels entries of thread-local memory owned by the kernel (kept outside this struct so that the
-                      // struct itself -- sp, base -- stays in registers)
+                      // struct itself -- sp, base -- stays in registers); entries [0, kStackCapacity - levels) are used
         WOST_DEV void init(uint2 *smem, int *overflow_flag, uint2 *spill_mem, int smem_levels = kSmemLevels)
         {
-            levels = smem_levels;
+            levels = smem_levels; // callers pass kMinSmemLevels..kSmemLevels
             spill = spill_mem;
             base = smem + threadIdx.x;
             stride = blockDim.x;
@@ -346,7 +350,7 @@ namespace wost
             const uint2 e = make_uint2(ref, __float_as_uint(d));
             if (__builtin_expect(sp < levels, 1))
                 base[sp * stride] = e;
-            else if (sp < levels + kSpillLevels)
+            else if (sp < kStackCapacity)
                 spill_store(spill, sp - levels, e);
             else
             {

@@ -569,7 +569,7 @@ namespace wost
         static const int env = []
         {
             const char *e = getenv("WOST_STACK_LEVELS");
-            return e ? std::max(1, std::min(kSmemLevels, atoi(e))) : 0;
+            return e ? std::max(kMinSmemLevels, std::min(kSmemLevels, atoi(e))) : 0;
         }();
         (void)F;
         return env > 0 ? env : (D == 2 ? 12 : kSmemLevels); // sweep (profiles/stack_levels_r2.json): 2D 12 (+1-2 %), 3D the full 20

@@ -316,3 +316,88 @@ def test_degenerate_meshes_match_oracle(oracle, name):
     io, do = so.nearest(on)
     ig, dg = sg.nearest(on)
     assert np.array_equal(bits(do), bits(dg)) and np.array_equal(io, ig)
+
+
+def _caterpillar_2d(log2n=17):
+    """A polyline soup whose LBVH is as deep as 2^log2n primitives allow. Twenty tiny segments sit in grid cells whose Morton code
+    has exactly ONE bit set (cell 2^j on one axis, 0 on the other): sorted, every split peels off one of them -> 20 levels. The
+    segments with indices 0, 1, 2, 4, ..., 2^(log2n-1) share cell (0, 0), hence one Morton code, so the 64-bit (code << 32 | index)
+    keys continue the chain through the index bits -> log2n more levels. Everything else fills distinct cells of the far quadrant."""
+    n = 1 << log2n
+    cell = np.zeros((n, 2), np.int64)
+    chain_idx = [0] + [1 << k for k in range(log2n)]
+    single_bit = [(1 << j, 0) for j in range(10)] + [(0, 1 << j) for j in range(10)]
+    free = [i for i in range(3, 3 + 4 * len(single_bit)) if i & (i - 1)][:len(single_bit)]   # indices that are not powers of two
+    used = set(chain_idx) | set(free)
+    for i, c in zip(free, single_bit):
+        cell[i] = c
+    rest = np.array([i for i in range(n) if i not in used])
+    k = np.arange(len(rest))
+    cell[rest, 0] = 512 + k % 512
+    cell[rest, 1] = 512 + (k // 512) % 512
+    ctr = (cell + 0.5) / 1024.0
+    h = 1.0 / 8192.0
+    a = ctr + np.array([-h, -h * 0.5])
+    b = ctr + np.array([h, h * 0.5])
+    # two anchors pin the whole box to [0, 1]^2 so that cell = floor(1024 * centroid) exactly
+    a[rest[-1]], b[rest[-1]] = (1.0 - 2 * h, 1.0 - h), (1.0, 1.0)
+    a[0], b[0] = (0.0, 0.0), (2 * h, h)
+    verts = np.concatenate([a, b], 0).astype(np.float32)
+    prims = np.stack([np.arange(n), np.arange(n) + n], 1).astype(np.int32)
+    return verts, prims
+
+
+def _max_leaf_depth(nodes):
+    parent = nodes[:, 0].astype(np.int64)
+    depth = np.zeros(len(nodes), np.int64)
+    n_internal = (len(nodes) - 1) // 2
+    # parents are not ordered by index in a Karras tree: relax until stable (depth <= 64 rounds)
+    for _ in range(80):
+        new = np.where(parent == 0xFFFFFFFF, 0, depth[np.minimum(parent, len(nodes) - 1)] + 1)
+        new[0] = 0
+        if np.array_equal(new, depth):
+            break
+        depth = new
+    return int(depth[n_internal:].max())
+
+
+def test_deep_caterpillar_tree_uses_the_spilled_stack_without_overflow(oracle):
+    """the traversal stack holds 64 entries in total (the reference's stack[64], core/query.cuh:250) whatever share of it
+    lives in shared memory -- 20 levels in the query kernels, 12 in the 2D walker. A degenerate tree (clustered Morton codes +
+    duplicated codes) of depth >= 36 forces queries deep into the thread-local spill area behind BOTH shares: closest point,
+    silhouette and ray results stay bit-identical to the oracle, no overflow is reported, and a short walker solve (12 shared
+    levels + spill) reproduces the oracle's film. (Depths of 57-64 need > 2^26 primitives with this builder: out of a test's reach;
+    the capacity arithmetic itself is a constexpr, kStackCapacity in csrc/lbvh.cuh.)"""
+    api = _api()
+    v, p = _caterpillar_2d(18)
+    so, sg = oracle.scene(2, v, p), api.Scene(2, v, p)
+    assert sg.used_morton64
+    no, _, _ = so.dump_bvh()
+    ng, _, _ = sg.dump_bvh()
+    assert np.array_equal(no, ng)
+    assert _max_leaf_depth(ng) >= 36
+    rng = np.random.RandomState(4)
+    q = np.concatenate([rng.rand(4000, 2) * 0.02, rng.rand(4000, 2), rng.rand(2000, 2) * 4 - 2]).astype(np.float32)
+    io, do = so.nearest(q)
+    ig, dg = sg.nearest(q)            # WOST_ERR_OVERFLOW would raise here
+    assert np.array_equal(io, ig) and np.array_equal(bits(do), bits(dg))
+    for flip in (False, True):
+        assert np.array_equal(bits(so.silhouette(q, flip)), bits(sg.silhouette(q, flip)))
+    d = rng.randn(len(q), 2).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    md = np.full(len(q), 3.0, np.float32)
+    ho, to, uvo, oo = so.ray(q, d, md)
+    hg, tg, uvg, og = sg.ray(q, d, md)
+    assert np.array_equal(ho, hg) and np.array_equal(oo, og) and np.array_equal(bits(to), bits(tg))
+    # the 2D persistent walker keeps 12 levels in shared memory: evaluation points right on top of the deep chain
+    from elaina_b200 import scenes
+    kw = dict(color_dirichlet=scenes.gray_pairs(rng.rand(len(v)).astype(np.float32)), color_neumann=None, grid_scale=0.01, grid_pos=(0.01, 0.01), grid_up=(0.0, 1.0),
+              aabb_min=(-0.5, -0.5), aabb_max=(1.5, 1.5))
+    oprob = dict(dim=2, dirichlet=so, neumann=None, **kw)
+    gprob = api.Problem(2, dirichlet=sg, neumann=None, **kw)
+    st = dict(frame_w=24, frame_h=24, max_walking_depth=12, samples_per_pixel=2, epsilon_shell=1e-4, seed=3)
+    sol_o, steps_o = oracle.solve_uniform(oprob, st)
+    it = api.UniformIntegrator(gprob, api.make_settings((24, 24), 12, 2, 1e-4, seed=3, spp_batch=1))
+    it.solve()                        # raises on a stack overflow
+    assert it.last_walk_steps == steps_o
+    assert np.array_equal(bits(it.film()[..., :3].reshape(-1, 3)), bits(sol_o))
