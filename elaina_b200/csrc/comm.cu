@@ -11,6 +11,8 @@
 #include "scene.cuh"
 
 #include <dlfcn.h>
+#include <fcntl.h>
+#include <cctype>
 #include <nccl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -237,6 +239,15 @@ extern "C"
             const char *port = getenv("MASTER_PORT");
             const char *tmp = getenv("TMPDIR");
             path = std::string(tmp && *tmp ? tmp : "/tmp") + "/wost_nccl_id_" + std::to_string((long)getppid()) + "_" + (port ? port : "0");
+            // per-launch nonce: a torchrun agent that restarts its workers keeps its pid and port, so a file left behind by a
+            // rank 0 that died before the unlink below must not be mistaken for this launch's id
+            for (const char *key : {"TORCHELASTIC_RUN_ID", "TORCHELASTIC_RESTART_COUNT", "OMPI_MCA_ess_base_jobid"})
+                if (const char *v = getenv(key))
+                {
+                    path += "_";
+                    for (const char *ch = v; *ch && ch - v < 64; ++ch)
+                        path += (isalnum((unsigned char)*ch) ? *ch : '-');
+                }
         }
         unsigned char id[128];
         if (rank == 0)
@@ -245,15 +256,18 @@ extern "C"
             if (rc != WOST_OK)
                 return rc;
             const std::string tmpf = path + ".tmp";
-            FILE *f = fopen(tmpf.c_str(), "wb");
-            if (!f || fwrite(id, 1, sizeof(id), f) != sizeof(id))
+            // the name is predictable: never write through a link someone else planted, never reuse a file we did not create
+            unlink(path.c_str());
+            unlink(tmpf.c_str());
+            const int fd = open(tmpf.c_str(), O_WRONLY | O_CREAT | O_EXCL | O_NOFOLLOW, 0600);
+            if (fd < 0 || write(fd, id, sizeof(id)) != (ssize_t)sizeof(id))
             {
-                if (f)
-                    fclose(f);
+                if (fd >= 0)
+                    close(fd);
                 set_last_error("wost_comm_create_from_env: cannot write " + tmpf);
                 return WOST_ERR_IO;
             }
-            fclose(f);
+            close(fd);
             if (rename(tmpf.c_str(), path.c_str()) != 0)
             {
                 set_last_error("wost_comm_create_from_env: cannot publish " + path);
@@ -266,12 +280,15 @@ extern "C"
             for (int attempt = 0; attempt < 6000 && !got; ++attempt) // 60 s
             {
                 struct stat sb;
-                if (stat(path.c_str(), &sb) == 0 && sb.st_size == (off_t)sizeof(id))
-                    if (FILE *f = fopen(path.c_str(), "rb"))
+                if (lstat(path.c_str(), &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size == (off_t)sizeof(id))
+                {
+                    const int fd = open(path.c_str(), O_RDONLY | O_NOFOLLOW);
+                    if (fd >= 0)
                     {
-                        got = fread(id, 1, sizeof(id), f) == sizeof(id);
-                        fclose(f);
+                        got = read(fd, id, sizeof(id)) == (ssize_t)sizeof(id);
+                        close(fd);
                     }
+                }
                 if (!got)
                     std::this_thread::sleep_for(std::chrono::milliseconds(10));
             }
@@ -403,10 +420,13 @@ extern "C"
                 return WOST_ERR_CUDA;
             }
             WOST_NCCL_TRY(api->GroupStart());
-            for (int q = 0; q < N; ++q)
+            ncclResult_t recv_rc = ncclSuccess; // a failed Recv must not leave the group open: close it, then report
+            for (int q = 0; q < N && recv_rc == ncclSuccess; ++q)
                 if (q != root)
-                    WOST_NCCL_TRY(api->Recv(c->stage.ptr + slot * q, (size_t)owned_row_count(H, sr, N, q) * rowf, ncclFloat, q, c->comm, st));
-            WOST_NCCL_TRY(api->GroupEnd());
+                    recv_rc = api->Recv(c->stage.ptr + slot * q, (size_t)owned_row_count(H, sr, N, q) * rowf, ncclFloat, q, c->comm, st);
+            const ncclResult_t end_rc = api->GroupEnd();
+            WOST_NCCL_TRY(recv_rc);
+            WOST_NCCL_TRY(end_rc);
             for (int q = 0; q < N; ++q)
                 if (q != root)
                     rows_kernel(c->stage.ptr + slot * q, owned_row_count(H, sr, N, q), q, 0);
