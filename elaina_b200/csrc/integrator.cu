@@ -11,6 +11,7 @@
 //               independent of scheduling: a pixel's samples of slot s are summed in sample order (== the oracle's
 //               order when S == 1), slots are summed in slot order by the resolve kernel.
 #include "integrator.cuh"
+#include <mutex>
 #include "walk.cuh"
 
 #include <algorithm>
@@ -537,8 +538,55 @@ namespace wost
     }
     // Blackwell L2 persistence for the top BVH levels: when the Dirichlet tree (fused records + leaf records) does not fit
     // the L2, the contiguous slab of its top levels (scene.cu: breadth-first record order, <= 32 MB) gets a persisting
-    // access-policy window on the integrator's stream; everything else on the stream is demoted to streaming, so the records
-    // every descent reads stay resident while leaf records and accumulators flow through. WOST_L2_PERSIST=0 disables it.
+    // access-policy window on the integrator's stream (hitRatio 1: every line of the window is marked persisting; missProp would
+    // only apply to window lines left out by a hitRatio < 1, so it has no effect here). Accesses outside the window keep the
+    // normal policy and compete for the rest of the L2. WOST_L2_PERSIST=0 disables it.
+    // The carve-out (cudaLimitPersistingL2CacheSize) is device-wide: it is raised to the largest window any live integrator of the
+    // device holds and never lowered under one; persisting lines are reset only when the LAST holder on the device goes away
+    // (cudaCtxResetPersistingL2Cache would otherwise drop the lines of every other live integrator, e.g. the c4-slices groups).
+    namespace
+    {
+        constexpr int kL2MaxDevices = 64;
+        std::mutex g_l2_mu;
+        size_t g_l2_limit[kL2MaxDevices] = {};
+        int g_l2_holders[kL2MaxDevices] = {};
+    } // namespace
+    static bool acquire_l2_carveout(int device, size_t bytes)
+    {
+        if (device < 0 || device >= kL2MaxDevices)
+            return false;
+        std::lock_guard<std::mutex> lock(g_l2_mu);
+        if (bytes > g_l2_limit[device])
+        {
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes) != cudaSuccess)
+            {
+                cudaGetLastError();
+                return false;
+            }
+            g_l2_limit[device] = bytes;
+        }
+        ++g_l2_holders[device];
+        return true;
+    }
+    void release_l2_window(int device)
+    {
+        if (device < 0 || device >= kL2MaxDevices)
+            return;
+        std::lock_guard<std::mutex> lock(g_l2_mu);
+        if (g_l2_holders[device] > 0 && --g_l2_holders[device] == 0)
+        {
+            int cur = 0;
+            cudaGetDevice(&cur);
+            if (cur != device)
+                cudaSetDevice(device);
+            cudaCtxResetPersistingL2Cache();
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0);
+            cudaGetLastError();
+            if (cur != device)
+                cudaSetDevice(cur);
+            g_l2_limit[device] = 0;
+        }
+    }
     static void apply_l2_window(wost_integrator *it)
     {
         it->l2_window_bytes = 0;
@@ -555,11 +603,8 @@ namespace wost
         if ((!force && sc->tnode_bytes() + leaf_bytes <= (size_t)l2) || max_persist <= 0 || max_window <= 0)
             return;
         const size_t bytes = std::min(std::min(sc->top_bytes(), (size_t)max_window), (size_t)max_persist);
-        if (bytes == 0 || cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes) != cudaSuccess)
-        {
-            cudaGetLastError();
+        if (bytes == 0 || !acquire_l2_carveout(it->device, bytes))
             return;
-        }
         cudaStreamAttrValue v;
         memset(&v, 0, sizeof(v));
         v.accessPolicyWindow.base_ptr = sc->d_tnodes.ptr;
@@ -570,7 +615,10 @@ namespace wost
         if (cudaStreamSetAttribute(it->stream, cudaStreamAttributeAccessPolicyWindow, &v) == cudaSuccess)
             it->l2_window_bytes = bytes;
         else
+        {
             cudaGetLastError();
+            release_l2_window(it->device);
+        }
     }
     template <int D, bool RefOrder, int F>
     static wost_status solve_persistent_f(wost_integrator *it, uint64_t *walk_steps);
@@ -1044,14 +1092,14 @@ extern "C"
             WOST_CUDA_TRY(cudaMemsetAsync(it->d_overflow.ptr + 1, 0, 2 * sizeof(int), it->stream));
         return WOST_OK;
     }
-    // diagnostics (library built with -DWOST_TRAV_DEBUG): closest-point trips [0..7] and queries [8..15] per decade of max |coordinate|
-    wost_status wost_debug_counters(wost_integrator *it, unsigned int *out16)
+    // diagnostics (library built with -DWOST_TRAV_DEBUG); the caller's buffer holds 48 words, see include/wost.h
+    wost_status wost_debug_counters(wost_integrator *it, unsigned int *out48)
     {
-        if (!it || !out16)
+        if (!it || !out48)
             return WOST_ERR_INVALID;
         // out: [0..15] trip / query counts, [16..47] 16 x 64-bit warp-cycle sums (trip iterations, tail iterations) per decade
-        WOST_CUDA_TRY(cudaMemcpy(out16, it->d_overflow.ptr + 8, 16 * sizeof(int), cudaMemcpyDeviceToHost));
-        WOST_CUDA_TRY(cudaMemcpy(out16 + 16, it->d_overflow.ptr + 32, 32 * sizeof(int), cudaMemcpyDeviceToHost));
+        WOST_CUDA_TRY(cudaMemcpy(out48, it->d_overflow.ptr + 8, 16 * sizeof(int), cudaMemcpyDeviceToHost));
+        WOST_CUDA_TRY(cudaMemcpy(out48 + 16, it->d_overflow.ptr + 32, 32 * sizeof(int), cudaMemcpyDeviceToHost));
         WOST_CUDA_TRY(cudaMemset(it->d_overflow.ptr + 8, 0, 88 * sizeof(int)));
         return WOST_OK;
     }

@@ -20,6 +20,8 @@ namespace wost
         float4 *b;
         uint32_t *c;
     };
+    // L2 persistence bookkeeping (integrator.cu): the persisting-L2 carve-out is a per-DEVICE limit shared by all integrators
+    void release_l2_window(int device);
 }
 
 struct wost_integrator
@@ -104,7 +106,7 @@ struct wost_integrator
         if (stream)
             cudaStreamDestroy(stream);
         if (l2_window_bytes)
-            cudaCtxResetPersistingL2Cache();
+            wost::release_l2_window(device);
     }
 };
 

@@ -210,9 +210,11 @@ extern "C"
     wost_status wost_film_device_ptr(wost_integrator *it, int channel, void **d_ptr);
     /* the same statistics for the closest-point queries of this integrator's solves and channel renders */
     wost_status wost_traversal_stats(wost_integrator *it, uint64_t *full_reference_order, uint64_t *restricted_second_pass, int reset);
-    /* diagnostics, meaningful only when the library was built with -DWOST_TRAV_DEBUG: closest-point trips [0..7] and queries
-     * [8..15] of this integrator per decade of the query's max |coordinate| (<600, <2e3, <1e4, ..., >=1e8); read and reset */
-    wost_status wost_debug_counters(wost_integrator *it, unsigned int *out16);
+    /* diagnostics, meaningful only when the library was built with -DWOST_TRAV_DEBUG. The caller provides 48 words:
+     * closest-point trips [0..7] and queries [8..15] of this integrator per decade of the query's max |coordinate|
+     * (<600, <2e3, <1e4, ..., >=1e8), then [16..47] = 16 little-endian 64-bit sums of warp cycles (8 decades of trip iterations,
+     * 8 of tail iterations); read and reset */
+    wost_status wost_debug_counters(wost_integrator *it, unsigned int *out48);
     /* bytes of top-level LBVH records this integrator pinned in L2 (cudaAccessPolicyWindow on its stream; 0 when the tree
      * fits the L2 or WOST_L2_PERSIST=0) -- north_star (2), no reference counterpart (the reference leaves L2 to the hardware) */
     wost_status wost_l2_window_bytes(wost_integrator *it, uint64_t *bytes);
