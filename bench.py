@@ -158,7 +158,10 @@ def cpu_oracle_sample(wl, budget_s=12.0, nthreads=0, keep_field=False):
     return total_steps / max(total_t, 1e-9), cores, sample, total_steps, total_t, first
 
 
-def run_reference_cuda(wl, spp, timeout=600):
+REF_CUDA_RECORD = os.path.join(ROOT, "baseline", "_ref", "last_reference_cuda.json")  # written by --impl reference, read by the repo arm
+
+
+def run_reference_cuda(wl, spp, timeout=600, integrator="uniform"):
     """the reference's own CUDA elaina-exec on this box's GPU, same workload through the same conf.json keys."""
     ref_bin = os.path.join(ROOT, "baseline", "_ref", "elaina-exec-ref")
     if not os.path.exists(ref_bin):
@@ -175,9 +178,9 @@ def run_reference_cuda(wl, spp, timeout=600):
     from elaina_b200 import workloads as wls
     case_dir = tempfile.mkdtemp(prefix="b1_bench_")
     try:
-        conf = wls.write_case(wl, case_dir, integrator="uniform", exp_name="ref", spp=spp)
+        conf = wls.write_case(wl, case_dir, integrator=integrator, exp_name="ref", spp=spp)
         r = b1_run.run_reference(conf, case_dir, "ref", timeout)
-        out = {"rc": r["rc"], "walk_steps": r["walk_steps"], "duration_ms": r["duration_ms"], "spp": spp,
+        out = {"rc": r["rc"], "walk_steps": r["walk_steps"], "duration_ms": r["duration_ms"], "spp": spp, "integrator": integrator,
                "sample": "whole frame at %d spp through baseline/_ref/elaina-exec-ref (reference sources built by baseline/build_ref_cuda.sh, "
                          "walk-step counter patch only), duration = result.json (exec.cu:157-158)" % spp}
         if r["walk_steps"] and r["duration_ms"]:
@@ -225,13 +228,47 @@ def run_reference_arm(args, wl, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t_total / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": wl["desc"], "note": "the reference walker is CUDA-only (no CPU path); this arm times the CPU oracle port -- pinned against the "
+            "config": {"workload": wl["desc"], "integrator": "uniform",
+                       "sample": "CPU arm: " + sample + "; reference_cuda: the whole frame at reduced spp (a rate, walk-steps/s)",
+                       "note": "the reference walker is CUDA-only (no CPU path); this arm times the CPU oracle port -- pinned against the "
                        "reference's own CUDA build, tests/test_oracle_b1_pin.py -- on all host threads; reference_cuda = the reference's own binary on this box's GPU"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     if not args.no_reference_cuda:
         line["reference_cuda"] = run_reference_cuda(wl, spp=min(wl["spp"], 32))
+        record = {"workload": wl["name"], "box_time": time.time(), "head": line["reference_cuda"], "sub": []}
+        if args.workload == "c3" and args.spp == 0 and "value" in line["reference_cuda"]:
+            # the repo arm's sub-workloads (same names), at reduced spp: the reference's rate does not depend on spp beyond the
+            # guided integrator's training share, which train spp = spp / 4 keeps proportional
+            for name, integ, spp in (("c3", "guided", 32), ("c1", "uniform", 16)):
+                r = run_reference_cuda(workload(name), spp=spp, integrator=integ)
+                r["name"] = "%s-%s" % (name, integ)
+                record["sub"].append(r)
+            line["reference_cuda_sub"] = record["sub"]
+        try:
+            with open(REF_CUDA_RECORD, "w") as f:
+                json.dump(record, f)
+        except OSError:
+            pass
     print(json.dumps(line), flush=True)
+
+
+def vs_reference_cuda(head_value, sub):
+    """ratio of this arm's device-timed rates to the reference's own CUDA binary, when `--impl reference` ran on THIS box before
+    (the driver runs the reference arm first); None otherwise. Both are rates in walk-steps/s on the same workload."""
+    try:
+        rec = json.load(open(REF_CUDA_RECORD))
+    except Exception:
+        return None
+    if rec.get("workload") != "c3" or abs(time.time() - rec.get("box_time", 0)) > 6 * 3600 or "value" not in rec.get("head", {}):
+        return None
+    out = {"c3-uniform": {"ratio": head_value / rec["head"]["value"], "reference_cuda_value": rec["head"]["value"], "reference_spp": rec["head"].get("spp")}}
+    ours = {r.get("name"): r for r in sub}
+    for r in rec.get("sub", []):
+        if "value" in r and r.get("name") in ours:
+            out[r["name"]] = {"ratio": ours[r["name"]]["value"] / r["value"], "reference_cuda_value": r["value"], "reference_spp": r.get("spp")}
+    out["note"] = "device-timed walk-steps/s of this arm / walk-steps/s of baseline/_ref/elaina-exec-ref (result.json duration) measured earlier on this box"
+    return out
 
 
 # ----------------------------------------------------------------------------------------------------------------------
@@ -423,6 +460,20 @@ class Bench:
             roof["issue"] = {k: ip.get(k) for k in ("issue_active_pct", "inst_per_cycle_per_sm", "threads_per_instruction", "warp_instructions_per_walk_step",
                                                     "l2_hit_rate_pct", "l2_gbs_achieved", "registers_per_thread", "ctas_per_sm") if k in ip}
             roof["issue"]["source"] = ip.get("source")
+            # L2-resident tree: the HBM figure above is nominal. L2 bytes per walk-step come from the committed capture (lts sectors x
+            # 32 B), the rate from THIS run's kernel time; the denominators are measured by tools/l2_peak.cu (profiles/l2_peak.json):
+            # per-lane random 16-byte loads (the shape of the node fetches: every lane in another record) and fully coalesced loads
+            try:
+                lp = json.load(open(os.path.join(ROOT, "profiles", "l2_peak.json")))
+                l2_bytes_per_step = ip["l2_gbs_achieved"] * 1e9 * ip["kernel_ms_under_ncu"] * 1e-3 / ip["walk_steps_in_launch"]
+                l2_gbs = l2_bytes_per_step * steps_total / (kern_ms * 1e-3) / 1e9
+                roof["l2"] = {"achieved_gbs": l2_gbs, "l2_bytes_per_walk_step": l2_bytes_per_step,
+                              "peak_gbs": lp["random16"]["sector_gbs_best"], "frac": l2_gbs / lp["random16"]["sector_gbs_best"],
+                              "peak_coalesced_gbs": lp["warp512"]["sector_gbs_best"], "frac_of_coalesced": l2_gbs / lp["warp512"]["sector_gbs_best"],
+                              "source": "bytes per walk-step: committed ncu capture (not this run); kernel time: this run; peaks: profiles/l2_peak.json "
+                                        "(tools/l2_peak.cu on a B200 of this pool, %d MiB buffer, L1 bypassed)" % lp.get("buffer_mib", 32)}
+            except Exception:
+                pass
         rec = {"value": value, "unit": UNIT, "ms_per_step": dev_ms / steps, "steps": steps, "warmup": warmup,
                "config": {"workload": wl["desc"], "integrator": integrator,
                           "walk_mode": walk_mode if not guided else ("fused tcgen05 bounce kernel" if mlp_impl == 0 else "validation: SIMT MLP through HBM"),
@@ -547,6 +598,10 @@ def main():
             line["cpu_baseline"] = cpu
         if parity is not None:
             line["parity_check"] = parity
+        if world == 1 and default_run:
+            ratio = vs_reference_cuda(head["value"], sub)
+            if ratio is not None:
+                line["vs_reference_cuda"] = ratio
         print(json.dumps(line), flush=True)
     if world > 1:
         B.barrier()
