@@ -517,6 +517,48 @@ class Bench:
         return out
 
 
+    def parity_check_multi(self, wl, spp=8, spp_batch=4, band_rows=64):
+        """N > 1: the film the N ranks solve in interleaved row tiles and gather on rank 0, against a band of
+        rows rank 0 then solves ALONE (one shard, pixel range) at the same fixed spp_batch: pixel-keyed Philox streams + slot-ordered
+        accumulators make the two bit-identical. Collective: every rank calls it."""
+        api, wdist = self.api, self.wdist
+        W, H = wl["frame"]
+        dim = wl["dim"]
+
+        def problem():
+            g_d = api.Scene(dim, wl["dverts"], wl["dprims"])
+            g_n = api.Scene(dim, wl["nverts"], wl["nprims"]) if wl.get("nverts") is not None else None
+            return api.Problem(dim, dirichlet=g_d, neumann=g_n, **problem_kwargs(wl))
+        prob = problem()
+        st = api.make_settings((W, H), wl["depth"], spp, wl["eps"], seed=wl["seed"], spp_batch=spp_batch, **wdist.shard_kwargs(self.rank, self.world, stride_rows=4))
+        it = api.UniformIntegrator(prob, st)
+        it.solve()
+        self.comm.gather_film(it, 0, 0)
+        gathered = it.film()[..., :3].copy() if self.rank == 0 else None
+        it.close()
+        self.barrier()
+        out = None
+        if self.rank == 0:
+            r0 = (H - band_rows) // 2
+            r1 = r0 + band_rows
+            st1 = api.make_settings((W, H), wl["depth"], spp, wl["eps"], seed=wl["seed"], spp_batch=spp_batch, pixel_begin=r0 * W, pixel_end=r1 * W)
+            it1 = api.UniformIntegrator(prob, st1)
+            it1.solve()
+            alone = it1.film()[r0:r1, :, :3].reshape(-1, 3)
+            it1.close()
+            got = gathered[r0:r1].reshape(-1, 3)
+            m = wl["mask"][r0:r1].reshape(-1).astype(bool) if wl.get("mask") is not None else np.ones(len(got), bool)
+            out = {"ranks": self.world, "rows": [int(r0), int(r1)], "pixels": int(m.sum()), "spp": spp, "spp_batch": spp_batch,
+                   "bit_identical": bool(np.array_equal(got[m].view(np.uint32), alone[m].view(np.uint32))),
+                   "max_abs_diff": float(np.max(np.abs(got[m] - alone[m]))) if m.any() else 0.0,
+                   "nonzero_pixels": int((np.abs(got[m]).sum(1) > 0).sum()),
+                   "what": "film solved by %d ranks (interleaved 4-row tiles, wost_film_gather to rank 0) == the same rows solved by rank 0 alone, "
+                           "same seed and spp_batch" % self.world}
+        prob.close()
+        self.barrier()
+        return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -583,6 +625,9 @@ def main():
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         if band is not None:
             parity = B.parity_check(wl, band)
+
+    if world > 1 and default_run:
+        parity = B.parity_check_multi(wl)
 
     if rank == 0:
         line = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
