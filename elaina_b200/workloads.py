@@ -3,7 +3,7 @@
 `workload(name)` -> dict with the geometry / boundary data / evaluation grid / integrator settings of one configuration:
 
   c1        configs[0]: data/ladybug on its REAL geometry (61 476 Dirichlet segments + the 4-segment Neumann square,
-            tests/golden/scene_ladybug.npz), settings of data/ladybug/u.json (uniform) / n.json (guided): 1024^2, 1024 spp,
+            elaina_b200/data/scene_ladybug.npz), settings of data/ladybug/u.json (uniform) / n.json (guided): 1024^2, 1024 spp,
             depth 64, epsilonShell 1. The shipped color.json is missing from the reference snapshot: colours are
             synthesised per connected stroke (scenes.synth_stroke_colors, seeded).
   c2        configs[1]: data/fille real geometry (66 367 segments), depth 128, 4-level DenseGrid network (data/fille/n.json)
@@ -25,7 +25,8 @@ import numpy as np
 from . import scenes
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-GOLDEN = os.path.join(ROOT, "tests", "golden")
+GOLDEN = os.path.join(ROOT, "tests", "golden")  # only the NanoVDB test fixture of the "nvdb" demo workload below
+DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")  # the package owns its inputs (data/make_scene_fixtures.py wrote them)
 
 NETWORK_LADYBUG = {  # data/ladybug/n.json:49-81
     "encoding": {"otype": "DenseGrid", "n_levels": 8, "n_features_per_level": 4, "base_resolution": 8,
@@ -41,7 +42,7 @@ NETWORK_FILLE["encoding"].update(n_levels=4, base_resolution=4)
 
 
 def _shipped(name):
-    z = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
+    z = np.load(os.path.join(DATA, "scene_%s.npz" % name))
     return z["dverts"], z["dprims"], z["nverts"], z["nprims"]
 
 

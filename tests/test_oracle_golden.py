@@ -73,7 +73,7 @@ def test_survey_golden_table(oracle):
 @pytest.mark.parametrize("mode", [1, 0])
 def test_survey_golden_table_model_obj(oracle, mode):
     """the data/ladybug/model.obj rows (122 951 nodes, 61 476 objects, Morton collisions -> 64-bit keys)
-    on the shipped geometry (tests/golden/scene_ladybug.npz, the float32 vertices the reference's loader produces)."""
+    on the shipped geometry (elaina_b200/data/scene_ladybug.npz, the float32 vertices the reference's loader produces)."""
     from elaina_b200 import workloads
     dv, dp, _, _ = workloads._shipped("ladybug")
     oracle.set_math_mode(mode)
