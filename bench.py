@@ -274,9 +274,9 @@ def vs_reference_cuda(head_value, sub):
 # ----------------------------------------------------------------------------------------------------------------------
 def issue_profile(wl, guided, walk_mode):
     """issue-slot figures of the dominant kernel from the committed ncu capture of the same kernel (NOT measured in this run)"""
-    if guided or wl["name"] not in ("c3", "c3-small", "c5") or not walk_mode.startswith("persistent"):
-        return None  # the committed capture is of k_walk_persistent<2, lean variant> on the C3 geometry
-    for name in ("traffic_r2.json", "traffic_r1d.json"):
+    if guided or wl["name"] not in ("c3", "c3-small", "c5", "c4", "c4-slices") or not walk_mode.startswith("persistent"):
+        return None  # committed captures: k_walk_persistent<2, lean variant> on the C3 geometry, k_walk_persistent<3> on the 1.31 M-triangle C4 tree
+    for name in (("traffic_r3_c4.json",) if wl["name"].startswith("c4") else ("traffic_r2.json", "traffic_r1d.json")):
         p = os.path.join(ROOT, "profiles", name)
         if not os.path.exists(p):
             continue
@@ -456,7 +456,7 @@ class Bench:
         if ip is not None:
             roof["traffic"] = ip["dram_bytes_per_walk_step"] * steps_total / max(1, kern_launches)
             roof["traffic_source"] = "NOT measured in this run: DRAM bytes per walk-step of the committed ncu capture (%s) x this run's walk-steps per launch" % ip.get("source", "profiles/")
-            roof["bound_actual"] = "issue"
+            roof["bound_actual"] = ip.get("bound_actual", "issue")
             roof["issue"] = {k: ip.get(k) for k in ("issue_active_pct", "inst_per_cycle_per_sm", "threads_per_instruction", "warp_instructions_per_walk_step",
                                                     "l2_hit_rate_pct", "l2_gbs_achieved", "registers_per_thread", "ctas_per_sm") if k in ip}
             roof["issue"]["source"] = ip.get("source")
